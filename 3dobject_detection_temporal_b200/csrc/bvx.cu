@@ -1,0 +1,699 @@
+// bvx.cu -- host side of the C ABI declared in include/bvx.h.
+//
+// The library owns only per-handle workspace; inputs and outputs are caller
+// owned device memory (the *_host forms stage through pinned memory).  There is
+// no CPU fallback: without a CUDA device bvx_create fails with BVX_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "bvx.h"
+#include "bvx_kernels.cuh"
+
+using namespace bvx;
+
+static std::atomic<long long> g_launches{0};
+static thread_local std::string g_last_error;
+
+struct bvx_handle {
+    bvx_config cfg;
+    GridParams grid;
+    long long ncells;
+    int device;
+    // capacities
+    long long table_slots;
+    long long words_cap;
+    long long voxel_cap;   // max_frames * max_voxels
+    // device workspace
+    unsigned long long* table = nullptr;
+    int* slot = nullptr;
+    unsigned int* cand = nullptr;
+    unsigned int* first = nullptr;
+    int* wordrank = nullptr;
+    int* bucket = nullptr;
+    int* cnt = nullptr;
+    int2* ovf = nullptr;
+    int* counters = nullptr;
+    FrameDesc* d_frames = nullptr;
+    SegDesc* d_segs = nullptr;
+    FrameState* d_state = nullptr;
+    int* d_offsets_scratch = nullptr;  // frame_voxel_offsets when the caller passes none
+    size_t ws_bytes = 0;
+    int seg_cap = 0;
+    // descriptor upload
+    std::vector<FrameDesc> h_frames;
+    std::vector<SegDesc> h_segs;
+    std::vector<char> uploaded;  // byte image of the last uploaded layout
+    static const int kRing = 4;
+    char* pin[kRing] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t pin_ev[kRing];
+    size_t pin_bytes = 0;
+    int pin_next = 0;
+    // host-form staging
+    void* stage_in = nullptr;
+    size_t stage_in_bytes = 0;
+    void* stage_out = nullptr;
+    size_t stage_out_bytes = 0;
+    float* dev_points = nullptr;
+    size_t dev_points_bytes = 0;
+    float* dev_voxels = nullptr;
+    int* dev_coors = nullptr;
+    int* dev_num = nullptr;
+    int* dev_offs = nullptr;
+    size_t dev_out_voxels = 0;  // voxel capacity of the dev_* outputs
+    int dev_out_tf = 0;
+    std::string err;
+};
+
+static int fail(bvx_handle* h, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf;
+    g_last_error = buf;
+    return code;
+}
+
+#define CK(h, call)                                                                          \
+    do {                                                                                     \
+        cudaError_t e_ = (call);                                                             \
+        if (e_ != cudaSuccess)                                                               \
+            return fail(h, BVX_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                                 \
+    } while (0)
+
+template <typename T>
+static cudaError_t dalloc(bvx_handle* h, T** p, size_t count)
+{
+    const size_t bytes = count * sizeof(T);
+    cudaError_t e = cudaMalloc((void**)p, bytes ? bytes : 16);
+    if (e == cudaSuccess) h->ws_bytes += bytes;
+    return e;
+}
+
+static int ilog2_ceil(unsigned long long v)
+{
+    int l = 0;
+    while ((1ull << l) < v) ++l;
+    return l;
+}
+
+extern "C" int bvx_abi_version(void) { return BVX_ABI_VERSION; }
+extern "C" int64_t bvx_launch_count(void) { return g_launches.load(); }
+
+extern "C" const char* bvx_last_error(const bvx_handle* h)
+{
+    return h ? h->err.c_str() : g_last_error.c_str();
+}
+
+extern "C" int bvx_grid_size(const float vs[3], const float rg[6], int64_t out[3])
+{
+    if (!vs || !rg || !out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    for (int j = 0; j < 3; ++j) {
+        volatile float ext = rg[3 + j] - rg[j];
+        volatile float q = ext / vs[j];
+        if (!(vs[j] > 0.0f) || !std::isfinite(q))
+            return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "voxel_size[%d] must be positive and finite", j);
+        out[j] = (int64_t)rintf(q);  // half-to-even, like numpy.round
+    }
+    return BVX_OK;
+}
+
+extern "C" int bvx_host_alloc(void** out, size_t bytes)
+{
+    if (!out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    cudaError_t e = cudaMallocHost(out, bytes ? bytes : 16);
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+extern "C" int bvx_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+    return BVX_OK;
+}
+
+extern "C" int bvx_destroy(bvx_handle* h)
+{
+    if (!h) return BVX_OK;
+    cudaSetDevice(h->device);
+    cudaFree(h->table); cudaFree(h->slot); cudaFree(h->cand); cudaFree(h->first);
+    cudaFree(h->wordrank); cudaFree(h->bucket); cudaFree(h->cnt); cudaFree(h->ovf);
+    cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
+    cudaFree(h->d_offsets_scratch);
+    cudaFree(h->dev_points); cudaFree(h->dev_voxels); cudaFree(h->dev_coors);
+    cudaFree(h->dev_num); cudaFree(h->dev_offs);
+    for (int i = 0; i < bvx_handle::kRing; ++i) {
+        if (h->pin[i]) { cudaFreeHost(h->pin[i]); cudaEventDestroy(h->pin_ev[i]); }
+    }
+    if (h->stage_in) cudaFreeHost(h->stage_in);
+    if (h->stage_out) cudaFreeHost(h->stage_out);
+    delete h;
+    return BVX_OK;
+}
+
+extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
+{
+    if (!cfg || !out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return fail(nullptr, BVX_ERR_NO_DEVICE, "no CUDA device: this library has no CPU fallback");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "device %d out of range (have %d)", cfg->device, ndev);
+    if (cfg->max_num_points < 1 || cfg->max_voxels < 1 || cfg->max_points < 1 || cfg->max_frames < 1 ||
+        cfg->max_point_features < 3)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT,
+                    "max_num_points/max_voxels/max_points/max_frames must be >= 1 and max_point_features >= 3");
+    if (cfg->overflow_mode != BVX_OVERFLOW_BREAK && cfg->overflow_mode != BVX_OVERFLOW_CONTINUE)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad overflow_mode %d", cfg->overflow_mode);
+    if (cfg->grid_kind != BVX_GRID_HASHED && cfg->grid_kind != BVX_GRID_DENSE)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad grid_kind %d", cfg->grid_kind);
+    int64_t gs[3];
+    int rc = bvx_grid_size(cfg->voxel_size, cfg->point_cloud_range, gs);
+    if (rc) return rc;
+    for (int j = 0; j < 3; ++j)
+        if (gs[j] < 1 || gs[j] > (1 << 24))
+            return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "grid_size[%d] = %lld out of range", j, (long long)gs[j]);
+    const long long ncells = (long long)gs[0] * gs[1] * gs[2];
+    if (ncells >= (1ll << 31))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "grid has %lld cells; at most 2^31-1 supported", ncells);
+
+    bvx_handle* h = new (std::nothrow) bvx_handle();
+    if (!h) return fail(nullptr, BVX_ERR_CUDA, "out of host memory");
+    h->cfg = *cfg;
+    h->device = cfg->device;
+    h->ncells = ncells;
+    for (int j = 0; j < 3; ++j) {
+        h->grid.lo[j] = cfg->point_cloud_range[j];
+        h->grid.vs[j] = cfg->voxel_size[j];
+        h->grid.gs[j] = (int)gs[j];
+        h->grid.gsf[j] = (float)gs[j];
+    }
+    auto bail = [&](cudaError_t e, const char* what) {
+        int code = fail(nullptr, BVX_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+        bvx_destroy(h);
+        return code;
+    };
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e != cudaSuccess) return bail(e, "cudaSetDevice");
+    const long long np = cfg->max_points, nf = cfg->max_frames;
+    if (cfg->grid_kind == BVX_GRID_DENSE) h->table_slots = ncells * nf;
+    else h->table_slots = 2 * np + 1024 * nf;
+    h->words_cap = np / 32 + 2 * nf + 8;
+    h->voxel_cap = (long long)cfg->max_voxels * nf;
+    h->seg_cap = (int)std::max<long long>(nf, 64);
+    if ((e = dalloc(h, &h->table, (size_t)h->table_slots)) != cudaSuccess) return bail(e, "alloc table");
+    if ((e = dalloc(h, &h->slot, (size_t)np)) != cudaSuccess) return bail(e, "alloc slot");
+    if ((e = dalloc(h, &h->cand, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc cand");
+    if ((e = dalloc(h, &h->first, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc first");
+    if ((e = dalloc(h, &h->wordrank, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc wordrank");
+    if ((e = dalloc(h, &h->bucket, (size_t)h->voxel_cap * cfg->max_num_points)) != cudaSuccess) return bail(e, "alloc bucket");
+    if ((e = dalloc(h, &h->cnt, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc cnt");
+    if (cfg->max_num_points > kChainMaxT)
+        if ((e = dalloc(h, &h->ovf, (size_t)np)) != cudaSuccess) return bail(e, "alloc ovf");
+    if ((e = dalloc(h, &h->counters, 8)) != cudaSuccess) return bail(e, "alloc counters");
+    if ((e = dalloc(h, &h->d_frames, (size_t)nf)) != cudaSuccess) return bail(e, "alloc frames");
+    if ((e = dalloc(h, &h->d_segs, (size_t)h->seg_cap)) != cudaSuccess) return bail(e, "alloc segs");
+    if ((e = dalloc(h, &h->d_state, (size_t)nf)) != cudaSuccess) return bail(e, "alloc state");
+    if ((e = dalloc(h, &h->d_offsets_scratch, (size_t)nf + 1)) != cudaSuccess) return bail(e, "alloc offsets");
+    // one-time initialisation; every call leaves the workspace clean again
+    if ((e = cudaMemset(h->table, 0xFF, (size_t)h->table_slots * 8)) != cudaSuccess) return bail(e, "memset table");
+    {
+        const size_t nb = (size_t)h->voxel_cap * cfg->max_num_points;
+        std::vector<int> fillv(std::min<size_t>(nb, 1 << 20), kEmptyIdx);
+        for (size_t off = 0; off < nb; off += fillv.size()) {
+            const size_t c = std::min(fillv.size(), nb - off);
+            if ((e = cudaMemcpy(h->bucket + off, fillv.data(), c * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+                return bail(e, "init bucket");
+        }
+    }
+    if ((e = cudaMemset(h->cnt, 0, (size_t)h->voxel_cap * 4)) != cudaSuccess) return bail(e, "memset cnt");
+    if ((e = cudaMemset(h->counters, 0, 32)) != cudaSuccess) return bail(e, "memset counters");
+    h->pin_bytes = sizeof(FrameDesc) * (size_t)nf + sizeof(SegDesc) * (size_t)h->seg_cap;
+    for (int i = 0; i < bvx_handle::kRing; ++i) {
+        if ((e = cudaMallocHost((void**)&h->pin[i], h->pin_bytes)) != cudaSuccess) return bail(e, "alloc pinned ring");
+        if ((e = cudaEventCreateWithFlags(&h->pin_ev[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
+    }
+    if ((e = cudaDeviceSynchronize()) != cudaSuccess) return bail(e, "sync");
+    *out = h;
+    return BVX_OK;
+}
+
+extern "C" int bvx_workspace_bytes(const bvx_handle* h, size_t* out)
+{
+    if (!h || !out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    *out = h->ws_bytes;
+    return BVX_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Build the frame / segment descriptors for a call and upload them if they
+// differ from what the device already holds.
+struct FrameSpec {
+    const bvx_sweep* sweeps;  // k sweeps (host structs, device point pointers)
+    int k;
+    int with_dt;
+};
+
+static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
+                         int* max_n_out, int* max_words_out, bool* all_aligned)
+{
+    const int B = (int)frames.size();
+    h->h_frames.assign(B, FrameDesc());
+    h->h_segs.clear();
+    long long pt = 0, wd = 0, tb = 0;
+    int max_n = 0, max_words = 0;
+    *all_aligned = true;
+    for (int f = 0; f < B; ++f) {
+        FrameDesc& fd = h->h_frames[f];
+        fd.seg_begin = (int)h->h_segs.size();
+        fd.seg_count = frames[f].k;
+        long long n = 0;
+        for (int s = 0; s < frames[f].k; ++s) {
+            const bvx_sweep& sw = frames[f].sweeps[s];
+            if (sw.n < 0 || (sw.n > 0 && !sw.points))
+                return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d sweep %d: bad points/n", f, s);
+            SegDesc sd;
+            memset(&sd, 0, sizeof sd);
+            sd.pts = sw.points;
+            sd.n = sw.n;
+            sd.start = (int)n;
+            sd.has_transform = sw.has_transform ? 1 : 0;
+            sd.has_dt = frames[f].with_dt;
+            memcpy(sd.R, sw.R, sizeof sd.R);
+            memcpy(sd.t, sw.t, sizeof sd.t);
+            sd.dt = sw.dt;
+            if (((uintptr_t)sw.points & 15) != 0) *all_aligned = false;
+            h->h_segs.push_back(sd);
+            n += sw.n;
+        }
+        if (frames[f].k == 0) {  // empty frame still needs one (empty) segment
+            SegDesc sd;
+            memset(&sd, 0, sizeof sd);
+            h->h_segs.push_back(sd);
+            fd.seg_count = 1;
+        }
+        if (n > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
+        fd.n = (int)n;
+        fd.pt_off = (int)pt;
+        fd.word_off = (int)wd;
+        fd.nwords = (int)((n + 31) / 32);
+        fd.tbl_off = (unsigned long long)tb;
+        if (h->cfg.grid_kind == BVX_GRID_DENSE) {
+            fd.tbl_shift = -1;
+            fd.tbl_mask = 0xFFFFFFFFu;
+            tb += h->ncells;
+        } else {
+            int lg = std::max(10, ilog2_ceil((unsigned long long)n + 1));
+            if ((1ll << lg) > h->ncells && h->ncells >= 1024) {
+                // table never needs more slots than there are cells
+                lg = std::max(10, ilog2_ceil((unsigned long long)h->ncells + 1));
+            }
+            fd.tbl_shift = 32 - lg;
+            fd.tbl_mask = (1u << lg) - 1u;
+            tb += (1ll << lg);
+        }
+        pt += n;
+        wd += fd.nwords;
+        max_n = std::max(max_n, fd.n);
+        max_words = std::max(max_words, fd.nwords);
+    }
+    if (pt > h->cfg.max_points)
+        return fail(h, BVX_ERR_WORKSPACE, "%lld points exceed the handle capacity max_points=%d", pt, h->cfg.max_points);
+    if (B > h->cfg.max_frames)
+        return fail(h, BVX_ERR_WORKSPACE, "%d frames exceed the handle capacity max_frames=%d", B, h->cfg.max_frames);
+    if (tb > h->table_slots || wd > h->words_cap || (int)h->h_segs.size() > h->seg_cap)
+        return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, words %lld/%lld, segs %zu/%d)",
+                    tb, h->table_slots, wd, h->words_cap, h->h_segs.size(), h->seg_cap);
+    *max_n_out = max_n;
+    *max_words_out = max_words;
+
+    const size_t fb = sizeof(FrameDesc) * (size_t)B, sb = sizeof(SegDesc) * h->h_segs.size();
+    std::vector<char> img(fb + sb);
+    memcpy(img.data(), h->h_frames.data(), fb);
+    memcpy(img.data() + fb, h->h_segs.data(), sb);
+    if (img == h->uploaded) return BVX_OK;  // device already holds this layout
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cs);
+    if (cs != cudaStreamCaptureStatusNone)
+        return fail(h, BVX_ERR_BAD_ARGUMENT,
+                    "layout changed during stream capture: run the call once outside capture first");
+    const int r = h->pin_next;
+    h->pin_next = (r + 1) % bvx_handle::kRing;
+    CK(h, cudaEventSynchronize(h->pin_ev[r]));
+    memcpy(h->pin[r], img.data(), img.size());
+    CK(h, cudaMemcpyAsync(h->d_frames, h->pin[r], fb, cudaMemcpyHostToDevice, st));
+    CK(h, cudaMemcpyAsync(h->d_segs, h->pin[r] + fb, sb, cudaMemcpyHostToDevice, st));
+    CK(h, cudaEventRecord(h->pin_ev[r], st));
+    h->uploaded.swap(img);
+    return BVX_OK;
+}
+
+struct Outputs {
+    float* voxels;
+    int32_t* coors;
+    int32_t* num_points;
+    int32_t* frame_voxel_offsets;  // [B+1] device (may be null -> scratch)
+    int32_t* voxel_num;            // [1] device (single-frame form; may be null)
+    float* mean;
+    int mean_c;
+    int coor_cols;
+};
+
+static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int f_in, int f_out,
+                        int max_voxels, const Outputs& o, cudaStream_t st)
+{
+    const int B = (int)frames.size();
+    if (B < 1) return fail(h, BVX_ERR_BAD_ARGUMENT, "need at least one frame");
+    if (f_in < 3) return fail(h, BVX_ERR_BAD_ARGUMENT, "points need at least 3 features, got %d", f_in);
+    if (f_out > h->cfg.max_point_features)
+        return fail(h, BVX_ERR_WORKSPACE, "%d output features exceed max_point_features=%d", f_out,
+                    h->cfg.max_point_features);
+    const int cap = max_voxels > 0 ? max_voxels : h->cfg.max_voxels;
+    if (cap > h->cfg.max_voxels)
+        return fail(h, BVX_ERR_WORKSPACE, "max_voxels=%d exceeds the handle capacity %d", cap, h->cfg.max_voxels);
+    if (!o.voxels || !o.coors || !o.num_points)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "null output pointer");
+    if (((uintptr_t)o.voxels & 15) || ((uintptr_t)o.coors & 15))
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "voxels/coors must be 16-byte aligned");
+    if (o.mean && (o.mean_c < 1 || o.mean_c > f_out))
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "mean_channels=%d must be in [1, %d]", o.mean_c, f_out);
+    CK(h, cudaSetDevice(h->device));
+    int max_n = 0, max_words = 0;
+    bool aligned = true;
+    int rc = upload_layout(h, frames, st, &max_n, &max_words, &aligned);
+    if (rc) return rc;
+
+    Pipe p;
+    memset(&p, 0, sizeof p);
+    p.g = h->grid;
+    p.frames = h->d_frames;
+    p.segs = h->d_segs;
+    p.state = h->d_state;
+    p.table = h->table;
+    p.slot = h->slot;
+    p.cand = h->cand;
+    p.first = h->first;
+    p.wordrank = h->wordrank;
+    p.bucket = h->bucket;
+    p.cnt = h->cnt;
+    p.ovf = h->ovf;
+    p.counters = h->counters;
+    p.frame_voxel_offsets = o.frame_voxel_offsets ? o.frame_voxel_offsets : h->d_offsets_scratch;
+    p.nframes = B;
+    p.f_in = f_in;
+    p.f_out = f_out;
+    p.T = h->cfg.max_num_points;
+    p.cap = cap;
+    p.overflow_continue = h->cfg.overflow_mode == BVX_OVERFLOW_CONTINUE;
+    p.coor_cols = o.coor_cols;
+    p.ovf_cap = h->cfg.max_points;
+    p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
+    p.voxels = o.voxels;
+    p.coors = o.coors;
+    p.num_points = o.num_points;
+    p.mean_out = o.mean;
+    p.mean_c = o.mean_c;
+
+    const int T = p.T;
+    const int chunks = (max_n + kBlock - 1) / kBlock;
+    const int wchunks = (max_words + kBlock - 1) / kBlock;
+    if (chunks > 0) {
+        k_insert<<<dim3(chunks, B), kBlock, 0, st>>>(p);
+        k_verify<<<dim3(wchunks, B), kBlock, 0, st>>>(p);
+        g_launches += 2;
+    }
+    k_rank<<<B, kRankThreads, 0, st>>>(p);
+    g_launches += 1;
+    if (chunks > 0) {
+        k_slot<<<dim3(chunks, B), kBlock, 0, st>>>(p);
+        g_launches += 1;
+        if (T > kChainMaxT) {
+            const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
+            k_overflow<<<ob, kBlock, 0, st>>>(p);
+            g_launches += 1;
+        }
+    }
+    const int vt = std::max(1, kBlock / T);
+    const int tiles = (cap + vt - 1) / vt;
+    const size_t smem = (size_t)((vt * T + 3) & ~3) * 4 + (size_t)vt * T * f_out * 4;
+    if (smem > 200 * 1024)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", smem);
+    if (smem > 48 * 1024)
+        CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_gather<<<dim3(tiles + wchunks, B), kBlock, smem, st>>>(p, tiles, vt);
+    g_launches += 1;
+    if (o.voxel_num) {
+        CK(h, cudaMemcpyAsync(o.voxel_num, p.frame_voxel_offsets + B, 4, cudaMemcpyDeviceToDevice, st));
+    }
+    CK(h, cudaGetLastError());
+    return BVX_OK;
+}
+
+static bvx_sweep plain_sweep(const float* pts, int n)
+{
+    bvx_sweep s;
+    memset(&s, 0, sizeof s);
+    s.points = pts;
+    s.n = n;
+    return s;
+}
+
+extern "C" int bvx_generate(bvx_handle* h, const float* points, int32_t n, int32_t f, int32_t max_voxels,
+                            float* voxels, int32_t* coors, int32_t* num_points, int32_t* voxel_num,
+                            void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (n < 0 || (n > 0 && !points)) return fail(h, BVX_ERR_BAD_ARGUMENT, "bad points/n");
+    bvx_sweep s = plain_sweep(points, n);
+    std::vector<FrameSpec> fr(1, FrameSpec{&s, 1, 0});
+    Outputs o{voxels, coors, num_points, nullptr, voxel_num, nullptr, 0, 3};
+    return run_pipeline(h, fr, f, f, max_voxels, o, (cudaStream_t)stream);
+}
+
+extern "C" int bvx_generate_sweeps(bvx_handle* h, const bvx_sweep* sweeps, int32_t k, int32_t f_in,
+                                   int32_t max_voxels, float* voxels, int32_t* coors, int32_t* num_points,
+                                   int32_t* voxel_num, void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (k < 1 || !sweeps) return fail(h, BVX_ERR_BAD_ARGUMENT, "need at least one sweep");
+    std::vector<FrameSpec> fr(1, FrameSpec{sweeps, k, 1});
+    Outputs o{voxels, coors, num_points, nullptr, voxel_num, nullptr, 0, 3};
+    return run_pipeline(h, fr, f_in, f_in + 1, max_voxels, o, (cudaStream_t)stream);
+}
+
+extern "C" int bvx_generate_batched(bvx_handle* h, const float* points, const int32_t* offs, int32_t b,
+                                    int32_t f, int32_t max_voxels, float* voxels, int32_t* coors4,
+                                    int32_t* num_points, int32_t* frame_voxel_offsets, float* mean,
+                                    int32_t mean_c, void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (b < 1 || !offs) return fail(h, BVX_ERR_BAD_ARGUMENT, "need frame_offsets and b >= 1");
+    if (f < 3) return fail(h, BVX_ERR_BAD_ARGUMENT, "points need at least 3 features, got %d", f);
+    std::vector<bvx_sweep> sw(b);
+    std::vector<FrameSpec> fr(b);
+    for (int i = 0; i < b; ++i) {
+        if (offs[i + 1] < offs[i] || offs[i] < 0) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame_offsets must be non-decreasing");
+        sw[i] = plain_sweep(points + (size_t)offs[i] * f, offs[i + 1] - offs[i]);
+        if (sw[i].n > 0 && !points) return fail(h, BVX_ERR_BAD_ARGUMENT, "null points");
+        fr[i] = FrameSpec{&sw[i], 1, 0};
+    }
+    Outputs o{voxels, coors4, num_points, frame_voxel_offsets, nullptr, mean, mean_c, 4};
+    return run_pipeline(h, fr, f, f, max_voxels, o, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ host forms
+static bool is_pinned(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+static int ensure_host_buffers(bvx_handle* h, size_t in_bytes, size_t voxels, int tf)
+{
+    if (in_bytes > h->dev_points_bytes) {
+        cudaFree(h->dev_points);
+        h->dev_points = nullptr;
+        CK(h, cudaMalloc((void**)&h->dev_points, in_bytes));
+        h->dev_points_bytes = in_bytes;
+    }
+    if (voxels > h->dev_out_voxels || tf > h->dev_out_tf) {
+        cudaFree(h->dev_voxels); cudaFree(h->dev_coors); cudaFree(h->dev_num); cudaFree(h->dev_offs);
+        h->dev_voxels = nullptr; h->dev_coors = nullptr; h->dev_num = nullptr; h->dev_offs = nullptr;
+        const size_t v = std::max(voxels, h->dev_out_voxels);
+        const int t2 = std::max(tf, h->dev_out_tf);
+        CK(h, cudaMalloc((void**)&h->dev_voxels, v * t2 * 4));
+        CK(h, cudaMalloc((void**)&h->dev_coors, v * 16));
+        CK(h, cudaMalloc((void**)&h->dev_num, v * 4));
+        CK(h, cudaMalloc((void**)&h->dev_offs, ((size_t)h->cfg.max_frames + 1) * 4));
+        h->dev_out_voxels = v;
+        h->dev_out_tf = t2;
+    }
+    return BVX_OK;
+}
+
+static int stage_in(bvx_handle* h, const void* src, size_t bytes, cudaStream_t st)
+{
+    if (bytes == 0) return BVX_OK;
+    if (is_pinned(src)) {
+        CK(h, cudaMemcpyAsync(h->dev_points, src, bytes, cudaMemcpyHostToDevice, st));
+        return BVX_OK;
+    }
+    if (bytes > h->stage_in_bytes) {
+        if (h->stage_in) cudaFreeHost(h->stage_in);
+        h->stage_in = nullptr;
+        CK(h, cudaMallocHost(&h->stage_in, bytes));
+        h->stage_in_bytes = bytes;
+    }
+    CK(h, cudaStreamSynchronize(st));  // staging buffer may still feed an earlier copy
+    memcpy(h->stage_in, src, bytes);
+    CK(h, cudaMemcpyAsync(h->dev_points, h->stage_in, bytes, cudaMemcpyHostToDevice, st));
+    return BVX_OK;
+}
+
+// D2H of three result arrays; pinned destinations are written in place.
+static int stage_out(bvx_handle* h, void* dst[3], const void* src[3], const size_t bytes[3], cudaStream_t st)
+{
+    size_t need = 0;
+    bool pinned[3];
+    for (int i = 0; i < 3; ++i) {
+        pinned[i] = bytes[i] == 0 || is_pinned(dst[i]);
+        if (!pinned[i]) need += (bytes[i] + 255) & ~(size_t)255;
+    }
+    if (need > h->stage_out_bytes) {
+        if (h->stage_out) cudaFreeHost(h->stage_out);
+        h->stage_out = nullptr;
+        CK(h, cudaMallocHost(&h->stage_out, need));
+        h->stage_out_bytes = need;
+    }
+    size_t off = 0;
+    char* tmp[3] = {nullptr, nullptr, nullptr};
+    for (int i = 0; i < 3; ++i) {
+        if (bytes[i] == 0) continue;
+        if (pinned[i]) {
+            CK(h, cudaMemcpyAsync(dst[i], src[i], bytes[i], cudaMemcpyDeviceToHost, st));
+        } else {
+            tmp[i] = (char*)h->stage_out + off;
+            off += (bytes[i] + 255) & ~(size_t)255;
+            CK(h, cudaMemcpyAsync(tmp[i], src[i], bytes[i], cudaMemcpyDeviceToHost, st));
+        }
+    }
+    CK(h, cudaStreamSynchronize(st));
+    for (int i = 0; i < 3; ++i)
+        if (tmp[i]) memcpy(dst[i], tmp[i], bytes[i]);
+    return BVX_OK;
+}
+
+extern "C" int bvx_generate_batched_host(bvx_handle* h, const float* points, const int32_t* offs, int32_t b,
+                                         int32_t f, int32_t max_voxels, float* voxels, int32_t* coors4,
+                                         int32_t* num_points, int32_t* fvo_host, void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (b < 1 || !offs || !fvo_host) return fail(h, BVX_ERR_BAD_ARGUMENT, "need frame_offsets, b >= 1 and an offsets output");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(h, cudaSetDevice(h->device));
+    const int cap = max_voxels > 0 ? max_voxels : h->cfg.max_voxels;
+    const int T = h->cfg.max_num_points;
+    const size_t n = (size_t)offs[b];
+    int rc = ensure_host_buffers(h, n * f * 4, (size_t)cap * b, T * f);
+    if (rc) return rc;
+    if ((rc = stage_in(h, points, n * f * 4, st))) return rc;
+    rc = bvx_generate_batched(h, h->dev_points, offs, b, f, cap, h->dev_voxels, h->dev_coors, h->dev_num,
+                              h->dev_offs, nullptr, 0, st);
+    if (rc) return rc;
+    CK(h, cudaMemcpyAsync(fvo_host, h->dev_offs, ((size_t)b + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    const size_t m = (size_t)fvo_host[b];
+    void* dst[3] = {voxels, coors4, num_points};
+    const void* src[3] = {h->dev_voxels, h->dev_coors, h->dev_num};
+    const size_t bytes[3] = {m * T * f * 4, m * 16, m * 4};
+    return stage_out(h, dst, src, bytes, st);
+}
+
+extern "C" int bvx_generate_host(bvx_handle* h, const float* points, int32_t n, int32_t f, int32_t max_voxels,
+                                 float* voxels, int32_t* coors, int32_t* num_points, int32_t* voxel_num_host,
+                                 void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (!voxel_num_host || n < 0) return fail(h, BVX_ERR_BAD_ARGUMENT, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(h, cudaSetDevice(h->device));
+    const int cap = max_voxels > 0 ? max_voxels : h->cfg.max_voxels;
+    const int T = h->cfg.max_num_points;
+    int rc = ensure_host_buffers(h, (size_t)n * f * 4, (size_t)cap, T * f);
+    if (rc) return rc;
+    if ((rc = stage_in(h, points, (size_t)n * f * 4, st))) return rc;
+    rc = bvx_generate(h, h->dev_points, n, f, cap, h->dev_voxels, h->dev_coors, h->dev_num, h->dev_offs, st);
+    if (rc) return rc;
+    CK(h, cudaMemcpyAsync(voxel_num_host, h->dev_offs, 4, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    const size_t m = (size_t)*voxel_num_host;
+    void* dst[3] = {voxels, coors, num_points};
+    const void* src[3] = {h->dev_voxels, h->dev_coors, h->dev_num};
+    const size_t bytes[3] = {m * T * f * 4, m * 12, m * 4};
+    return stage_out(h, dst, src, bytes, st);
+}
+
+// ------------------------------------------------------------------ VFE / scatter
+extern "C" int bvx_mean_vfe(const float* voxels, const int32_t* num_points, int32_t m, int32_t t, int32_t f,
+                            int32_t c_out, int32_t simple, float* out, void* stream)
+{
+    if (m < 0 || t < 1 || f < 1 || c_out < 1 || c_out > f)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad mean_vfe shape m=%d t=%d f=%d c_out=%d", m, t, f, c_out);
+    if (simple && c_out < 4) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "SimpleVoxel needs c_out >= 4");
+    if (m == 0) return BVX_OK;
+    if (!voxels || !num_points || !out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    int vt = std::max(1, std::min(64, 8192 / (t * f)));
+    const size_t smem = ((size_t)vt * t * f + (size_t)vt * c_out) * 4;
+    if (smem > 200 * 1024) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "t*f too large for the VFE tile");
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_mean_vfe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
+    const int blocks = (m + vt - 1) / vt;
+    k_mean_vfe<<<blocks, kBlock, smem, (cudaStream_t)stream>>>(voxels, num_points, m, t, f, c_out, simple, vt, out);
+    g_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "k_mean_vfe launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+extern "C" int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m, int32_t c, int32_t b,
+                               int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream)
+{
+    if (m < 0 || c < 1 || b < 1 || d < 1 || ny < 1 || nx < 1)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad scatter shape");
+    if (!canvas || (m > 0 && (!feats || !coors4))) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    if (((uintptr_t)canvas & 15) || ((uintptr_t)coors4 & 15))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "canvas/coors must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t total = (size_t)b * c * d * ny * nx;
+    const size_t n4 = total >> 2;
+    const int ntail = (int)(total & 3);
+    const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
+    k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(canvas), n4, canvas + (n4 << 2), ntail);
+    g_launches += 1;
+    if (m > 0) {
+        const long long work = (long long)m * c;
+        k_scatter<<<(unsigned)((work + kBlock - 1) / kBlock), kBlock, 0, st>>>(
+            feats, reinterpret_cast<const int4*>(coors4), m, c, b, d, ny, nx, canvas);
+        g_launches += 1;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "scatter launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}

@@ -1,0 +1,344 @@
+"""``VoxelGenerator`` -- drop-in for ``spconv.utils.VoxelGenerator`` as the reference
+uses it (constructed at second/builder/voxel_builder.py:23-27; ``generate`` called
+inside the reference's ``prep_pointcloud``, wired at
+second/builder/dataset_builder.py:51-58 and second/core/inference.py:43-48).
+
+Same constructor keywords, same attributes (``voxel_size`` f32[3],
+``point_cloud_range`` f32[6], ``grid_size`` int64[3] xyz,
+``max_num_points_per_voxel``), same return tuple ``(voxels[M,T,F] f32,
+coordinates[M,3] i32 zyx, num_points_per_voxel[M] i32)``.  The work runs in
+hand-written sm_100a kernels behind the C ABI of include/bvx.h.
+
+* numpy in  -> numpy out (host form: H2D, kernels, D2H of the M result rows)
+* CUDA torch tensor in -> CUDA torch tensors out (no copies, caller's stream)
+
+There is no CPU fallback: without a GPU ``generate`` raises.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _lib
+
+
+def _as_f32x(v, n, name):
+    a = np.asarray(v, dtype=np.float32).reshape(-1)
+    if a.shape[0] != n:
+        raise ValueError(f"{name} must have {n} elements, got {a.shape[0]}")
+    return a
+
+
+def _is_torch(x):
+    return type(x).__module__.split(".")[0] == "torch"
+
+
+class VoxelGenerator:
+    def __init__(self, voxel_size, point_cloud_range, max_num_points, max_voxels=20000,
+                 overflow="break", grid="hashed", device=None):
+        if overflow not in _lib.OVERFLOW:
+            raise ValueError(f"overflow must be 'break' or 'continue', got {overflow!r}")
+        if grid not in _lib.GRID:
+            raise ValueError(f"grid must be 'hashed' or 'dense', got {grid!r}")
+        self._voxel_size = _as_f32x(voxel_size, 3, "voxel_size")
+        self._point_cloud_range = _as_f32x(point_cloud_range, 6, "point_cloud_range")
+        self._max_num_points = int(max_num_points)
+        self._max_voxels = int(max_voxels)
+        if self._max_num_points < 1 or self._max_voxels < 1:
+            raise ValueError("max_num_points and max_voxels must be >= 1")
+        self._overflow = overflow
+        self._grid = grid
+        self._device = device
+        lib = _lib.load()
+        gs = (ctypes.c_int64 * 3)()
+        _lib.check(lib.bvx_grid_size(
+            self._voxel_size.ctypes.data_as(ctypes.POINTER(ctypes.c_float)),
+            self._point_cloud_range.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), gs))
+        self._grid_size = np.array(list(gs), dtype=np.int64)
+        self._handle = None
+        self._cap = dict(max_points=0, max_frames=0, max_voxels=0, max_point_features=0)
+
+    # ---- attributes the reference reads (second_builder.py:17-18, train.py:135)
+    @property
+    def voxel_size(self):
+        return self._voxel_size
+
+    @property
+    def point_cloud_range(self):
+        return self._point_cloud_range
+
+    @property
+    def grid_size(self):
+        return self._grid_size
+
+    @property
+    def max_num_points_per_voxel(self):
+        return self._max_num_points
+
+    @property
+    def overflow(self):
+        return self._overflow
+
+    # ---- handle management
+    def _device_index(self):
+        if self._device is None:
+            return 0
+        if isinstance(self._device, int):
+            return self._device
+        idx = getattr(self._device, "index", None)
+        return 0 if idx is None else int(idx)
+
+    def _ensure(self, n_points, n_frames, max_voxels, n_feat, device_index=None):
+        c = self._cap
+        dev = self._device_index() if device_index is None else device_index
+        if (self._handle is not None and n_points <= c["max_points"] and n_frames <= c["max_frames"]
+                and max_voxels <= c["max_voxels"] and n_feat <= c["max_point_features"]
+                and dev == c.get("device")):
+            return self._handle
+        self.close()
+        need = dict(max_points=max(n_points, 1), max_frames=max(n_frames, 1),
+                    max_voxels=max(max_voxels, self._max_voxels),
+                    max_point_features=max(n_feat, 4))
+        cap = {}
+        for k, v in need.items():
+            old = c[k]
+            # first allocation is exact; later growth is geometric so that frames of
+            # slowly varying size do not re-create the handle every call
+            cap[k] = v if old == 0 else (old if v <= old else int(v * 1.25) + 1)
+        cap["max_voxels"] = max(need["max_voxels"], c["max_voxels"])
+        cap["max_point_features"] = max(need["max_point_features"], c["max_point_features"])
+        cap["device"] = dev
+        cfg = _lib.BvxConfig()
+        cfg.voxel_size[:] = self._voxel_size.tolist()
+        cfg.point_cloud_range[:] = self._point_cloud_range.tolist()
+        cfg.max_num_points = self._max_num_points
+        cfg.max_voxels = cap["max_voxels"]
+        cfg.overflow_mode = _lib.OVERFLOW[self._overflow]
+        cfg.grid_kind = _lib.GRID[self._grid]
+        cfg.max_points = cap["max_points"]
+        cfg.max_frames = cap["max_frames"]
+        cfg.max_point_features = cap["max_point_features"]
+        cfg.device = dev
+        h = ctypes.c_void_p()
+        _lib.check(_lib.load().bvx_create(ctypes.byref(cfg), ctypes.byref(h)))
+        self._handle = h
+        self._cap = cap
+        return h
+
+    def close(self):
+        if self._handle is not None:
+            _lib.load().bvx_destroy(self._handle)
+            self._handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def workspace_bytes(self):
+        if self._handle is None:
+            return 0
+        out = ctypes.c_size_t()
+        _lib.check(_lib.load().bvx_workspace_bytes(self._handle, ctypes.byref(out)), self._handle)
+        return int(out.value)
+
+    # ---- VoxelGenerator.generate
+    def generate(self, points, max_voxels=None):
+        """(voxels, coordinates, num_points_per_voxel) of one frame."""
+        max_voxels = int(max_voxels or self._max_voxels)
+        if _is_torch(points):
+            return self._generate_device(points, max_voxels)
+        pts = np.ascontiguousarray(points, dtype=np.float32)
+        if pts.ndim != 2 or pts.shape[1] < 3:
+            raise ValueError(f"points must be [N, F>=3], got {pts.shape}")
+        n, f = pts.shape
+        h = self._ensure(n, 1, max_voxels, f)
+        t = self._max_num_points
+        voxels = np.empty((max_voxels, t, f), dtype=np.float32)
+        coors = np.empty((max_voxels, 3), dtype=np.int32)
+        num = np.empty((max_voxels,), dtype=np.int32)
+        m = ctypes.c_int32(0)
+        _lib.check(_lib.load().bvx_generate_host(
+            h, pts.ctypes.data, n, f, max_voxels, voxels.ctypes.data, coors.ctypes.data,
+            num.ctypes.data, ctypes.byref(m), None), h)
+        return voxels[:m.value], coors[:m.value], num[:m.value]
+
+    def _generate_device(self, points, max_voxels, padded=False):
+        import torch
+        if not points.is_cuda:
+            raise ValueError("torch points must live on a CUDA device (numpy arrays take the host form)")
+        if points.dtype != torch.float32 or points.dim() != 2 or points.shape[1] < 3:
+            raise ValueError("points must be a float32 [N, F>=3] tensor")
+        points = points.contiguous()
+        n, f = points.shape
+        dev = points.device
+        h = self._ensure(n, 1, max_voxels, f, dev.index)
+        t = self._max_num_points
+        with torch.cuda.device(dev):
+            voxels = torch.empty((max_voxels, t, f), dtype=torch.float32, device=dev)
+            coors = torch.empty((max_voxels, 3), dtype=torch.int32, device=dev)
+            num = torch.empty((max_voxels,), dtype=torch.int32, device=dev)
+            cnt = torch.empty((1,), dtype=torch.int32, device=dev)
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(_lib.load().bvx_generate(
+                h, points.data_ptr(), n, f, max_voxels, voxels.data_ptr(), coors.data_ptr(),
+                num.data_ptr(), cnt.data_ptr(), st), h)
+        if padded:
+            return voxels, coors, num, cnt
+        m = int(cnt.item())
+        return voxels[:m], coors[:m], num[:m]
+
+    def generate_padded(self, points, max_voxels=None):
+        """Device form without the host sync: padded outputs + device count [1]."""
+        return self._generate_device(points, int(max_voxels or self._max_voxels), padded=True)
+
+    # ---- temporal input (north star)
+    def generate_sweeps(self, sweeps, max_voxels=None):
+        """``sweeps``: list of (points[N_s, F_in], R[3,3] or None, t[3] or None, dt).
+        Key frame first.  The merged cloud (xyz transformed, dt appended) is never
+        materialised; F_out = F_in + 1.  numpy or CUDA tensors (all the same kind)."""
+        max_voxels = int(max_voxels or self._max_voxels)
+        if len(sweeps) < 1:
+            raise ValueError("need at least one sweep")
+        use_torch = _is_torch(sweeps[0][0])
+        import torch
+        if use_torch:
+            dev = sweeps[0][0].device
+        else:
+            dev = torch.device("cuda", self._device_index())
+        keep, arr = [], (_lib.BvxSweep * len(sweeps))()
+        f_in = None
+        total = 0
+        for i, (pts, R, t, dt) in enumerate(sweeps):
+            if use_torch:
+                p = pts.contiguous()
+                if p.dtype != torch.float32 or not p.is_cuda:
+                    raise ValueError("sweep points must be float32 CUDA tensors")
+            else:
+                p = torch.from_numpy(np.ascontiguousarray(pts, dtype=np.float32)).to(dev)
+            if p.dim() != 2 or p.shape[1] < 3:
+                raise ValueError("sweep points must be [N, F>=3]")
+            if f_in is None:
+                f_in = int(p.shape[1])
+            elif f_in != p.shape[1]:
+                raise ValueError("all sweeps need the same feature count")
+            keep.append(p)
+            arr[i].points = p.data_ptr()
+            arr[i].n = int(p.shape[0])
+            arr[i].has_transform = 0 if R is None else 1
+            Rm = np.eye(3, dtype=np.float32) if R is None else np.asarray(R, dtype=np.float32).reshape(3, 3)
+            tv = np.zeros(3, dtype=np.float32) if t is None else np.asarray(t, dtype=np.float32).reshape(3)
+            arr[i].R[:] = Rm.reshape(-1).tolist()
+            arr[i].t[:] = tv.tolist()
+            arr[i].dt = float(np.float32(dt))
+            total += int(p.shape[0])
+        f_out = f_in + 1
+        h = self._ensure(total, 1, max_voxels, f_out, dev.index)
+        tt = self._max_num_points
+        with torch.cuda.device(dev):
+            voxels = torch.empty((max_voxels, tt, f_out), dtype=torch.float32, device=dev)
+            coors = torch.empty((max_voxels, 3), dtype=torch.int32, device=dev)
+            num = torch.empty((max_voxels,), dtype=torch.int32, device=dev)
+            cnt = torch.empty((1,), dtype=torch.int32, device=dev)
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(_lib.load().bvx_generate_sweeps(
+                h, arr, len(sweeps), f_in, max_voxels, voxels.data_ptr(), coors.data_ptr(),
+                num.data_ptr(), cnt.data_ptr(), st), h)
+            m = int(cnt.item())
+        out = voxels[:m], coors[:m], num[:m]
+        if not use_torch:
+            out = tuple(o.cpu().numpy() for o in out)
+        return out
+
+    # ---- B frames per call (+ the voxel part of merge_second_batch)
+    def generate_batched(self, points, frame_offsets=None, max_voxels=None, mean_channels=0,
+                         padded=False):
+        """Voxelize B frames in one call.
+
+        ``points``: list of per-frame arrays, or one [sum N, F] array/tensor with
+        ``frame_offsets`` [B+1].  Returns ``(voxels[sumM,T,F], coordinates[sumM,4]
+        (b,z,y,x), num_points[sumM], frame_voxel_offsets[B+1])`` (+ mean features
+        [sumM, mean_channels] when ``mean_channels > 0``: the mean VFE fused into the
+        gather kernel).  ``padded=True`` (device form) skips the host sync and returns
+        capacity-sized buffers.
+        """
+        max_voxels = int(max_voxels or self._max_voxels)
+        if isinstance(points, (list, tuple)):
+            if len(points) == 0:
+                raise ValueError("need at least one frame")
+            sizes = [int(p.shape[0]) for p in points]
+            frame_offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+            if _is_torch(points[0]):
+                import torch
+                points = torch.cat([p.contiguous() for p in points], dim=0)
+            else:
+                points = np.concatenate([np.asarray(p, dtype=np.float32) for p in points], axis=0)
+        if frame_offsets is None:
+            raise ValueError("frame_offsets required with a concatenated points array")
+        offs = np.ascontiguousarray(frame_offsets, dtype=np.int32)
+        b = offs.shape[0] - 1
+        if b < 1 or offs[0] != 0:
+            raise ValueError("frame_offsets must be [B+1] starting at 0")
+        offs_p = offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+        t = self._max_num_points
+        lib = _lib.load()
+        if _is_torch(points):
+            import torch
+            if not points.is_cuda or points.dtype != torch.float32 or points.dim() != 2:
+                raise ValueError("points must be a float32 CUDA [N, F] tensor")
+            points = points.contiguous()
+            n, f = points.shape
+            if int(offs[-1]) != n:
+                raise ValueError("frame_offsets[-1] must equal the number of points")
+            dev = points.device
+            h = self._ensure(n, b, max_voxels, f, dev.index)
+            cap = b * max_voxels
+            with torch.cuda.device(dev):
+                voxels = torch.empty((cap, t, f), dtype=torch.float32, device=dev)
+                coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
+                num = torch.empty((cap,), dtype=torch.int32, device=dev)
+                fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
+                mean = (torch.empty((cap, mean_channels), dtype=torch.float32, device=dev)
+                        if mean_channels > 0 else None)
+                st = torch.cuda.current_stream(dev).cuda_stream
+                _lib.check(lib.bvx_generate_batched(
+                    h, points.data_ptr(), offs_p, b, f, max_voxels, voxels.data_ptr(), coors.data_ptr(),
+                    num.data_ptr(), fvo.data_ptr(), mean.data_ptr() if mean is not None else None,
+                    mean_channels, st), h)
+            if padded:
+                return (voxels, coors, num, fvo) + ((mean,) if mean is not None else ())
+            m = int(fvo[-1].item())
+            return (voxels[:m], coors[:m], num[:m], fvo) + ((mean[:m],) if mean is not None else ())
+        if mean_channels:
+            raise ValueError("mean_channels is only available in the device form")
+        pts = np.ascontiguousarray(points, dtype=np.float32)
+        n, f = pts.shape
+        if int(offs[-1]) != n:
+            raise ValueError("frame_offsets[-1] must equal the number of points")
+        h = self._ensure(n, b, max_voxels, f)
+        cap = b * max_voxels
+        voxels = np.empty((cap, t, f), dtype=np.float32)
+        coors = np.empty((cap, 4), dtype=np.int32)
+        num = np.empty((cap,), dtype=np.int32)
+        fvo = np.empty((b + 1,), dtype=np.int32)
+        _lib.check(lib.bvx_generate_batched_host(
+            h, pts.ctypes.data, offs_p, b, f, max_voxels, voxels.ctypes.data, coors.ctypes.data,
+            num.ctypes.data, fvo.ctypes.data, None), h)
+        m = int(fvo[-1])
+        return voxels[:m], coors[:m], num[:m], fvo
+
+
+def pinned_empty(shape, dtype=np.float32):
+    """numpy array backed by pinned host memory (bvx_host_alloc); the host forms
+    DMA straight from/to it.  Keep the returned array alive while it is in use."""
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    p = ctypes.c_void_p()
+    _lib.check(_lib.load().bvx_host_alloc(ctypes.byref(p), max(nbytes, 16)))
+    buf = (ctypes.c_char * max(nbytes, 16)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[id(buf)] = (buf, p)
+    return arr
+
+
+_PINNED = {}

@@ -1,0 +1,191 @@
+/*
+ * bvx.h -- C ABI of the B200-native voxelization hot path.
+ *
+ * Drop-in boundary for jhkohpav/3dobject_detection_temporal (a SECOND fork).
+ * The reference reaches this path through a Python object protocol, not a C
+ * ABI; each entry point below names the reference interface it replaces
+ * (paths relative to the reference root).  The Python mirror of that protocol
+ * (VoxelGenerator / VoxelFeatureExtractorV3 / PointPillarsScatter) lives in
+ * 3dobject_detection_temporal_b200/ and binds these symbols with ctypes; the
+ * stub a reference maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / pybind types.
+ *   - every `*_dev` / unqualified data pointer is a DEVICE pointer owned by the
+ *     caller (torch allocates all inputs and outputs); the library owns only
+ *     the per-handle workspace.  `*_host` entry points take HOST pointers.
+ *   - all work is enqueued on the given cudaStream_t (passed as void*); the
+ *     device entry points never synchronise.
+ *   - return value: 0 = BVX_OK, otherwise a bvx_status; the message is
+ *     available from bvx_last_error().  Nothing throws across the ABI.
+ *   - one handle per (device, stream); not thread-safe.
+ *   - there is NO CPU fallback: every entry point needs a CUDA device.
+ */
+#ifndef BVX_H_
+#define BVX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BVX_ABI_VERSION 1
+
+typedef enum bvx_status {
+    BVX_OK = 0,
+    BVX_ERR_BAD_ARGUMENT = 1,   /* Python side raises ValueError   */
+    BVX_ERR_CUDA = 2,           /* Python side raises RuntimeError */
+    BVX_ERR_WORKSPACE = 3,      /* capacity given at create time exceeded */
+    BVX_ERR_NO_DEVICE = 4
+} bvx_status;
+
+/* What happens when voxel number `max_voxels` would be created:
+ * BREAK    = stop scanning, every later point is dropped (spconv v1.0 /
+ *            second.pytorch v1.5, the era this fork derives from) -- default.
+ * CONTINUE = skip only points that would open a new voxel (later upstream). */
+#define BVX_OVERFLOW_BREAK 0
+#define BVX_OVERFLOW_CONTINUE 1
+
+/* Cell -> voxel lookup structure.  HASHED: open-addressing table sized by the
+ * number of points (L2 resident).  DENSE: one entry per grid cell, the layout
+ * of the reference's cached `coor_to_voxelidx` grid. */
+#define BVX_GRID_HASHED 0
+#define BVX_GRID_DENSE 1
+
+typedef struct bvx_config {
+    float voxel_size[3];         /* x, y, z                                   */
+    float point_cloud_range[6];  /* x0 y0 z0 x1 y1 z1                         */
+    int32_t max_num_points;      /* T: points kept per voxel                  */
+    int32_t max_voxels;          /* capacity AND default per-frame cap        */
+    int32_t overflow_mode;       /* BVX_OVERFLOW_*                            */
+    int32_t grid_kind;           /* BVX_GRID_*                                */
+    int32_t max_points;          /* capacity: points per call (all frames)    */
+    int32_t max_frames;          /* capacity: frames per call                 */
+    int32_t max_point_features;  /* capacity: output channels F_out per point */
+    int32_t device;              /* CUDA device ordinal                       */
+} bvx_config;
+
+typedef struct bvx_handle bvx_handle;
+
+/* One sweep of a temporal frame (new functionality named by the
+ * north star -- the reference voxelizes current and previous frame separately,
+ * second/pytorch/train_2st_spatio.py:182-195).  Row i of the virtual merged
+ * cloud is (R @ xyz + t, feat[3:f_in], dt) with
+ *   x' = ((r00*x + r01*y) + r02*z) + tx   in fp32, no FMA contraction.
+ * has_transform == 0 copies xyz verbatim (key frame). */
+typedef struct bvx_sweep {
+    const float* points;   /* device, [n, f_in] row-major */
+    int32_t n;
+    int32_t has_transform;
+    float R[9];            /* row-major 3x3, sweep -> key frame */
+    float t[3];
+    float dt;              /* seconds, appended as channel f_in */
+} bvx_sweep;
+
+/* Replaces spconv.utils.VoxelGenerator.__init__ as constructed at
+ * second/builder/voxel_builder.py:23-27.  Allocates the workspace. */
+int bvx_create(const bvx_config* cfg, bvx_handle** out);
+int bvx_destroy(bvx_handle* h);
+
+/* VoxelGenerator.grid_size: round((range[3:]-range[:3])/voxel_size) in fp32,
+ * half-to-even, x y z (same formula: second/kittiviewer/viewer.py:468-469;
+ * consumers: second/pytorch/builder/second_builder.py:17-18). */
+int bvx_grid_size(const float voxel_size[3], const float point_cloud_range[6],
+                  int64_t out_xyz[3]);
+
+/* Bytes of device workspace the handle owns. */
+int bvx_workspace_bytes(const bvx_handle* h, size_t* out);
+
+/* Replaces VoxelGenerator.generate(points, max_voxels) ->
+ * (voxels, coordinates, num_points_per_voxel)   [called inside the reference's
+ * prep_pointcloud; wired at second/builder/dataset_builder.py:51-58 and
+ * second/core/inference.py:43-48; twin call sites
+ * second/kittiviewer/viewer.py:385-392, 451-457].
+ *   points     [n, f]              f32
+ *   voxels     [max_voxels, T, f]  f32, rows [0, M) written, zero padded
+ *   coors      [max_voxels, 3]     i32 (z, y, x)
+ *   num_points [max_voxels]        i32
+ *   voxel_num  [1]                 i32, M written on device
+ * max_voxels <= 0 selects the handle default. */
+int bvx_generate(bvx_handle* h, const float* points, int32_t n, int32_t f,
+                 int32_t max_voxels, float* voxels, int32_t* coors,
+                 int32_t* num_points, int32_t* voxel_num, void* stream);
+
+/* Temporal input: K sweeps merged in-kernel with the dt channel appended; the
+ * merged cloud is never written to memory.  Outputs as bvx_generate with
+ * f_out = f_in + 1. */
+int bvx_generate_sweeps(bvx_handle* h, const bvx_sweep* sweeps_host, int32_t k,
+                        int32_t f_in, int32_t max_voxels, float* voxels,
+                        int32_t* coors, int32_t* num_points, int32_t* voxel_num,
+                        void* stream);
+
+/* B frames per call; replaces B calls to generate() plus the voxel part of the
+ * reference's collate merge_second_batch (imported second/pytorch/train.py:17):
+ * outputs are concatenated in frame order and coors carry the batch index,
+ * [sum M, 4] i32 (b, z, y, x) (second/pytorch/models/voxelnet.py:285).
+ *   points               [sum n_b, f], frame b = rows [off[b], off[b+1])
+ *   frame_offsets_host   [b + 1] HOST int32
+ *   voxels               [b * max_voxels, T, f]   (capacity; [0, sum M) written)
+ *   coors4               [b * max_voxels, 4]
+ *   num_points           [b * max_voxels]
+ *   frame_voxel_offsets  [b + 1] DEVICE int32, exclusive prefix of M_b
+ *   mean_features        optional [b * max_voxels, mean_channels] f32: the mean
+ *                        VFE fused into the gather (NULL to skip)            */
+int bvx_generate_batched(bvx_handle* h, const float* points,
+                         const int32_t* frame_offsets_host, int32_t b, int32_t f,
+                         int32_t max_voxels, float* voxels, int32_t* coors4,
+                         int32_t* num_points, int32_t* frame_voxel_offsets,
+                         float* mean_features, int32_t mean_channels,
+                         void* stream);
+
+/* Host-buffer forms (numpy in, numpy out -- the exact shape of the reference's
+ * CPU call).  Copies H2D, runs the device path, copies the M result rows D2H,
+ * synchronises the stream and returns M in *voxel_num_host.  Pinned buffers
+ * (bvx_host_alloc) are used in place; pageable ones go through a pinned
+ * staging buffer owned by the handle. */
+int bvx_generate_host(bvx_handle* h, const float* points_host, int32_t n,
+                      int32_t f, int32_t max_voxels, float* voxels_host,
+                      int32_t* coors_host, int32_t* num_points_host,
+                      int32_t* voxel_num_host, void* stream);
+int bvx_generate_batched_host(bvx_handle* h, const float* points_host,
+                              const int32_t* frame_offsets_host, int32_t b,
+                              int32_t f, int32_t max_voxels, float* voxels_host,
+                              int32_t* coors4_host, int32_t* num_points_host,
+                              int32_t* frame_voxel_offsets_host, void* stream);
+int bvx_host_alloc(void** out, size_t bytes);  /* pinned host memory */
+int bvx_host_free(void* p);
+
+/* Replaces VoxelFeatureExtractorV3.forward(features, num_voxels)
+ * (second/pytorch/models/voxel_encoder.py:201-206): out[v, c] =
+ * sum_t voxels[v, t, c] / num_points[v] for c < c_out.  The reference
+ * hard-codes c_out = 4; c_out = f keeps the dt channel of temporal input.
+ * simple_voxel != 0 emits SimpleVoxel's [ |xy|_2, z, refl ] instead
+ * (voxel_encoder.py:221-228; needs c_out >= 4, output has 3 channels). */
+int bvx_mean_vfe(const float* voxels, const int32_t* num_points, int32_t m,
+                 int32_t t, int32_t f, int32_t c_out, int32_t simple_voxel,
+                 float* out, void* stream);
+
+/* PointPillarsScatter / SparseConvTensor.dense() replacement behind the middle
+ * extractor protocol forward(voxel_features, coors, batch_size) ->
+ * [N, C*D, H, W] (second/pytorch/models/middle.py:513-526); math of
+ * torchplus.scatter_nd (torchplus/ops/array_ops.py:7-20): zeros, then
+ * canvas[b, c*D + z, y, x] = feats[i, c] for coors4[i] = (b, z, y, x).
+ * The zero fill is part of the call. */
+int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m,
+                    int32_t c, int32_t b, int32_t d, int32_t ny, int32_t nx,
+                    float* canvas, void* stream);
+
+/* Message of the last failing call on this handle (or, with h == NULL, of the
+ * last failing handle-less call on this thread). */
+const char* bvx_last_error(const bvx_handle* h);
+
+/* Kernel launches enqueued by this library since load (for gpu_launches). */
+int64_t bvx_launch_count(void);
+int bvx_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BVX_H_ */

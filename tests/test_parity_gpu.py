@@ -1,0 +1,306 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU
+oracle on the same seeded inputs.  Bar: bit-exact for voxels / coordinates /
+counts / ordering (integer work and pure copies; the sweep transform has a fixed
+operation order without FMA, so it is bit-exact too); 1e-6 relative for the
+mean VFE and BEV canvases (fp32 sums)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+KITTI = dict(voxel_size=[0.05, 0.05, 0.1], point_cloud_range=[0, -40, -3, 70.4, 40, 1])
+PILLAR = dict(voxel_size=[0.16, 0.16, 4], point_cloud_range=[0, -39.68, -3, 69.12, 39.68, 1])
+NUSC = dict(voxel_size=[0.1, 0.1, 0.2], point_cloud_range=[-51.2, -51.2, -5, 51.2, 51.2, 3])
+COARSE = dict(voxel_size=[2.0, 2.0, 2.0], point_cloud_range=[-8, -8, -2, 8, 8, 2])
+
+
+def _eq(got, want, what=""):
+    got = [g.cpu().numpy() if hasattr(g, "cpu") else np.asarray(g) for g in got]
+    assert got[0].shape == want[0].shape, f"{what}: M {got[0].shape} vs {want[0].shape}"
+    assert np.array_equal(got[1], want[1]), f"{what}: coordinates differ"
+    assert np.array_equal(got[2], want[2]), f"{what}: num_points differ"
+    assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), f"{what}: voxels differ"
+
+
+def _pair(pkg, oracle, grid_cfg, T, cap, overflow="break", grid="hashed"):
+    g = pkg.VoxelGenerator(grid_cfg["voxel_size"], grid_cfg["point_cloud_range"], T, cap,
+                           overflow=overflow, grid=grid)
+    o = oracle.OracleVoxelGenerator(grid_cfg["voxel_size"], grid_cfg["point_cloud_range"], T, cap,
+                                    overflow=overflow)
+    return g, o
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+@pytest.mark.parametrize("grid", ["hashed", "dense"])
+@pytest.mark.parametrize("n,cap", [(1, 10), (31, 10), (33, 1000), (1000, 50), (5000, 700), (20011, 3000),
+                                   (20011, 100000)])
+def test_kitti_shaped_device_form(pkg, oracle, synth, overflow, grid, n, cap):
+    pts = synth.lidar_frame(n, "kitti", seed=n)
+    g, o = _pair(pkg, oracle, KITTI, 5, cap, overflow, grid)
+    want = o.generate(pts)
+    got = g.generate(torch.from_numpy(pts).cuda())
+    _eq(got, want, f"n={n} cap={cap} {overflow} {grid}")
+    # same handle again: the workspace must have cleaned itself
+    got = g.generate(torch.from_numpy(pts).cuda())
+    _eq(got, want, "second call")
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_host_form_numpy_roundtrip(pkg, oracle, synth, overflow):
+    pts = synth.lidar_frame(30000, "kitti", seed=3)
+    g, o = _pair(pkg, oracle, KITTI, 5, 4000, overflow)
+    got = g.generate(pts)
+    assert isinstance(got[0], np.ndarray) and got[1].dtype == np.int32 and got[2].dtype == np.int32
+    _eq(got, o.generate(pts), "host form")
+    # call-time cap overrides the default like the reference's generate(points, max_voxels)
+    _eq(g.generate(pts, 1234), o.generate(pts, 1234), "host form, call-time cap")
+    # pinned input is used in place
+    pp = pkg.pinned_empty(pts.shape, np.float32)
+    pp[:] = pts
+    _eq(g.generate(pp), o.generate(pts), "pinned host form")
+
+
+def test_unshuffled_ring_order(pkg, oracle, synth):
+    pts = synth.lidar_frame(40000, "kitti", seed=5, shuffle=False)
+    for overflow in ("break", "continue"):
+        g, o = _pair(pkg, oracle, KITTI, 5, 6000, overflow)
+        _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"ring order {overflow}")
+
+
+@pytest.mark.parametrize("f", [3, 4, 5, 7])
+def test_feature_counts(pkg, oracle, f):
+    rng = np.random.default_rng(f)
+    pts = rng.uniform(-9, 9, size=(7001, f)).astype(np.float32)
+    g, o = _pair(pkg, oracle, COARSE, 6, 100)
+    _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"F={f}")
+    _eq(g.generate(pts), o.generate(pts), f"F={f} host")
+
+
+def test_empty_and_all_outside(pkg, oracle):
+    g, o = _pair(pkg, oracle, COARSE, 4, 50)
+    empty = np.zeros((0, 4), np.float32)
+    got = g.generate(empty)
+    assert got[0].shape == (0, 4, 4) and got[1].shape == (0, 3) and got[2].shape == (0,)
+    got = g.generate(torch.from_numpy(empty).cuda())
+    assert got[0].shape == (0, 4, 4)
+    outside = np.full((100, 4), 1000.0, np.float32)
+    _eq(g.generate(torch.from_numpy(outside).cuda()), o.generate(outside), "all outside")
+
+
+def test_boundaries_nan_inf_negzero(pkg, oracle):
+    vs, rg = COARSE["voxel_size"], COARSE["point_cloud_range"]
+    rows = []
+    for x in (-8.0, -8.000001, 7.999999, 8.0, -0.0, 0.0, 2.0, 1.9999999, np.nan, np.inf, -np.inf, 1e30):
+        rows.append([x, 0.5, 0.5, 1.0])
+        rows.append([0.5, x, 0.5, 2.0])
+        rows.append([0.5, 0.5, x if abs(x) != 8.0 else x / 4, 3.0])
+    pts = np.array(rows, dtype=np.float32)
+    g, o = _pair(pkg, oracle, COARSE, 3, 50)
+    _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), "boundaries")
+    # fp32 division corner: values on voxel edges of the KITTI grid
+    g2, o2 = _pair(pkg, oracle, KITTI, 5, 20000)
+    k = np.arange(0, 1408, dtype=np.float32)
+    edge = np.stack([k * np.float32(0.05), np.zeros_like(k), np.zeros_like(k), k], 1)
+    edge = np.concatenate([edge, np.nextafter(edge, np.float32(100)), np.nextafter(edge, np.float32(-100))])
+    edge = np.ascontiguousarray(edge, dtype=np.float32)
+    _eq(g2.generate(torch.from_numpy(edge).cuda()), o2.generate(edge), "voxel edges")
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_cap_exactly_and_one_over(pkg, oracle, overflow):
+    # 12 distinct cells, several points each, interleaved
+    rng = np.random.default_rng(0)
+    cells = rng.permutation(np.repeat(np.arange(12), 7))
+    pts = np.stack([cells % 4 * 2.0 - 7, cells // 4 * 2.0 - 7, np.zeros(len(cells)),
+                    np.arange(len(cells))], 1).astype(np.float32)
+    for cap in (11, 12, 13, 1):
+        g, o = _pair(pkg, oracle, COARSE, 5, cap, overflow)
+        _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"cap={cap} {overflow}")
+
+
+@pytest.mark.parametrize("T", [1, 2, 5, 8, 9, 35, 100])
+def test_crowded_voxels_truncation(pkg, oracle, T):
+    # everything in a handful of voxels: exercises max_points truncation in input order
+    rng = np.random.default_rng(T)
+    n = 30000
+    pts = rng.uniform(-3.9, 3.9, size=(n, 4)).astype(np.float32)  # 16 cells of the coarse grid
+    pts[:, 2] = 0.5
+    g, o = _pair(pkg, oracle, COARSE, T, 40)
+    _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"T={T}")
+    one = np.tile(np.array([[0.5, 0.5, 0.5, 0.0]], np.float32), (5000, 1))
+    one[:, 3] = np.arange(5000)
+    _eq(g.generate(torch.from_numpy(one).cuda()), o.generate(one), f"T={T} single voxel")
+    _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"T={T} repeat")
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_pillars_T100(pkg, oracle, synth, overflow):
+    for shuffle in (True, False):
+        pts = synth.lidar_frame(60000, "kitti", seed=11, shuffle=shuffle)
+        g, o = _pair(pkg, oracle, PILLAR, 100, 5000, overflow)
+        _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"pillars shuffle={shuffle}")
+        g, o = _pair(pkg, oracle, PILLAR, 12, 12000, overflow)   # many voxels over T
+        _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"pillars T=12 shuffle={shuffle}")
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_sweeps(pkg, oracle, synth, overflow):
+    sweeps = synth.lidar_sweeps(4, 9000, "nuscenes", 100, 0.05)
+    merged = oracle.merge_sweeps(sweeps)
+    assert merged.shape == (36000, 5)
+    g, o = _pair(pkg, oracle, NUSC, 10, 9000, overflow)
+    want = o.generate(merged)
+    dsw = [(torch.from_numpy(p).cuda(), R, t, dt) for p, R, t, dt in sweeps]
+    _eq(g.generate_sweeps(dsw), want, "sweeps device")
+    _eq(g.generate_sweeps(sweeps), want, "sweeps numpy")
+    # ragged sweep sizes incl. an empty sweep, F_in = 5
+    rng = np.random.default_rng(1)
+    rag = []
+    for s, n in enumerate([1000, 0, 37, 4001]):
+        p = rng.uniform(-50, 50, size=(n, 5)).astype(np.float32)
+        p[:, 2] = rng.uniform(-5, 3, size=n)
+        R, t = synth.sweep_transform(s)
+        rag.append((p, None if s == 0 else R, None if s == 0 else t, 0.05 * s))
+    g, o = _pair(pkg, oracle, NUSC, 3, 2000, overflow)
+    _eq(g.generate_sweeps(rag), o.generate(oracle.merge_sweeps(rag)), "ragged sweeps")
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_batched(pkg, oracle, synth, overflow):
+    sizes = [5000, 0, 33, 12001, 1, 7000]
+    frames = [synth.lidar_frame(n, "kitti", seed=40 + i) for i, n in enumerate(sizes)]
+    g, o = _pair(pkg, oracle, KITTI, 5, 2500, overflow)
+    wv, wc, wn, woff = o.generate_batched(frames)
+    dv, dc, dn, doff = g.generate_batched([torch.from_numpy(f).cuda() for f in frames])
+    assert np.array_equal(doff.cpu().numpy(), woff)
+    _eq((dv, dc, dn), (wv, wc, wn), "batched device")
+    hv, hc, hn, hoff = g.generate_batched(frames)
+    assert np.array_equal(hoff, woff)
+    _eq((hv, hc, hn), (wv, wc, wn), "batched host")
+    # fused mean VFE == separate module == oracle
+    out = g.generate_batched([torch.from_numpy(f).cuda() for f in frames], mean_channels=4)
+    mean = out[4].cpu().numpy()
+    want = oracle.mean_vfe(wv, wn)
+    np.testing.assert_allclose(mean, want, rtol=1e-6, atol=0)
+    sep = pkg.VoxelFeatureExtractorV3()(dv, dn).cpu().numpy()
+    assert np.array_equal(sep.view(np.uint32), mean.view(np.uint32))
+
+
+def test_handle_growth_and_reuse(pkg, oracle, synth):
+    g, o = _pair(pkg, oracle, KITTI, 5, 2000)
+    for n in (1000, 50000, 200, 80000, 50000):
+        pts = synth.lidar_frame(n, "kitti", seed=n)
+        _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"growth n={n}")
+    _eq(g.generate(pts, 9000), o.generate(pts, 9000), "bigger cap")
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg3"])
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_full_size_single_frame_configs(pkg, oracle, synth, name, overflow):
+    c = synth.CONFIGS[name]
+    pts = synth.make_frames(name, 1)[0]
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"],
+                           overflow=overflow)
+    o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
+                                    c["max_voxels"], overflow=overflow)
+    _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), name)
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg5"])
+def test_full_size_sweep_configs(pkg, oracle, synth, name):
+    c = synth.CONFIGS[name]
+    sweeps = synth.make_sweeps(name)
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"])
+    o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
+                                    c["max_voxels"])
+    dsw = [(torch.from_numpy(p).cuda(), R, t, dt) for p, R, t, dt in sweeps]
+    _eq(g.generate_sweeps(dsw), o.generate(oracle.merge_sweeps(sweeps)), name)
+
+
+def test_full_size_cfg4_batch_properties(pkg, oracle, synth):
+    """BASELINE cfg4 (64 x 120k): full oracle comparison on 8 frames, size-independent
+    properties on all 64 (per-frame results identical to single-frame calls, sorted
+    offsets, counts in [1, T], every kept point inside its voxel)."""
+    c = synth.CONFIGS["cfg4"]
+    frames = synth.make_frames("cfg4", 64)
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"])
+    o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
+                                    c["max_voxels"])
+    dframes = [torch.from_numpy(f).cuda() for f in frames]
+    v, cc, n, off = g.generate_batched(dframes)
+    off = off.cpu().numpy()
+    assert off[0] == 0 and np.all(np.diff(off) == c["max_voxels"])   # the cap is hit in every frame
+    vn, cn, nn = v.cpu().numpy(), cc.cpu().numpy(), n.cpu().numpy()
+    assert nn.min() >= 1 and nn.max() <= c["max_num_points"]
+    for b in range(0, 64, 8):
+        wv, wc, wn = o.generate(frames[b])
+        sl = slice(off[b], off[b + 1])
+        assert np.all(cn[sl, 0] == b)
+        _eq((vn[sl], cn[sl, 1:], nn[sl]), (wv, wc, wn), f"cfg4 frame {b}")
+    # every kept point lies inside the voxel it was assigned to
+    vs = np.asarray(c["voxel_size"], np.float32)
+    lo = np.asarray(c["point_cloud_range"][:3], np.float32)
+    slot = np.arange(c["max_num_points"])[None, :] < nn[:, None]
+    cell = np.floor((vn[..., :3] - lo) / vs).astype(np.int32)[..., ::-1]
+    assert np.all((cell == cn[:, None, 1:])[slot])
+    assert np.all(vn[~slot] == 0)
+
+
+def test_mean_vfe_and_scatter_golden(pkg, oracle, golden_dir):
+    import os
+    z = np.load(os.path.join(golden_dir, "vfe_reference.npz"))
+    for tag in ("t5f4", "t100f4", "t10f5"):
+        vox, num = z[f"{tag}_voxels"], z[f"{tag}_num"]
+        got = pkg.VoxelFeatureExtractorV3()(torch.from_numpy(vox).cuda(), torch.from_numpy(num).cuda())
+        np.testing.assert_allclose(got.cpu().numpy(), z[f"{tag}_v3"], rtol=1e-6, atol=1e-6)
+        got = pkg.SimpleVoxel()(torch.from_numpy(vox).cuda(), torch.from_numpy(num).cuda())
+        np.testing.assert_allclose(got.cpu().numpy(), z[f"{tag}_simple"], rtol=1e-6, atol=1e-6)
+        # all channels (keeps dt for temporal input) vs oracle
+        f = vox.shape[2]
+        got = pkg.VoxelFeatureExtractorV3(num_output_channels=f)(torch.from_numpy(vox).cuda(),
+                                                                 torch.from_numpy(num).cuda())
+        np.testing.assert_allclose(got.cpu().numpy(), oracle.mean_vfe(vox, num, f), rtol=1e-6, atol=0)
+    z = np.load(os.path.join(golden_dir, "scatter_reference.npz"))
+    for tag in ("pp_c4", "pp_c64", "d2_c3"):
+        b, c, d, h, w = (int(x) for x in z[f"{tag}_shape"])
+        mod = pkg.PointPillarsScatter([1, d, h, w, c], num_input_features=c)
+        got = mod(torch.from_numpy(z[f"{tag}_feats"]).cuda(), torch.from_numpy(z[f"{tag}_coors"]).cuda(), b)
+        assert got.shape == (b, c * d, h, w)
+        assert np.array_equal(got.cpu().numpy(), z[f"{tag}_canvas"])
+
+
+def test_pillar_pipeline_to_canvas(pkg, oracle, synth):
+    c = synth.CONFIGS["cfg3"]
+    frames = [synth.lidar_frame(50000, "kitti", seed=90 + i) for i in range(3)]
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"])
+    o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
+                                    c["max_voxels"])
+    v, cc, n, off = g.generate_batched([torch.from_numpy(f).cuda() for f in frames])
+    wv, wc, wn, woff = o.generate_batched(frames)
+    _eq((v, cc, n), (wv, wc, wn), "pillars batched")
+    feat = pkg.VoxelFeatureExtractorV3()(v, n)
+    gx, gy, gz = (int(x) for x in g.grid_size)
+    canvas = pkg.PointPillarsScatter([1, gz, gy, gx, 4])(feat, cc, 3)
+    want = oracle.scatter_bev(oracle.mean_vfe(wv, wn), wc, 3, gz, gy, gx)
+    np.testing.assert_allclose(canvas.cpu().numpy(), want, rtol=1e-6, atol=0)
+    # backward of the scatter is the gather of the written cells
+    feat2 = feat.clone().requires_grad_(True)
+    out = pkg.PointPillarsScatter([1, gz, gy, gx, 4])(feat2, cc, 3)
+    out.sum().backward()
+    assert torch.all(feat2.grad == 1)
+
+
+def test_errors(pkg):
+    g = pkg.VoxelGenerator([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 100)
+    with pytest.raises(ValueError):
+        g.generate(np.zeros((10, 2), np.float32))
+    with pytest.raises(ValueError):
+        g.generate(torch.zeros((10, 4)))            # CPU tensor
+    with pytest.raises(ValueError):
+        pkg.VoxelGenerator([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, overflow="wrap")
+    with pytest.raises(ValueError):
+        pkg.VoxelGenerator([0.0, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5)
+    with pytest.raises(RuntimeError):
+        pkg.VoxelFeatureExtractorV3()(torch.zeros((3, 5, 4)), torch.ones(3, dtype=torch.int32))
