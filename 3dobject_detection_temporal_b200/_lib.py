@@ -16,6 +16,8 @@ BVX_ERR_CUDA = 2
 BVX_ERR_WORKSPACE = 3
 BVX_ERR_NO_DEVICE = 4
 
+PROFILE_SLOTS = 8
+KERNEL_NAMES = ["k_insert", "k_verify", "", "k_slot", "k_overflow", "k_gather", "", ""]
 OVERFLOW = {"break": 0, "continue": 1}
 GRID = {"hashed": 0, "dense": 1}
 
@@ -69,6 +71,9 @@ SYMBOLS = {
     "bvx_host_free": (ctypes.c_int, [_vp]),
     "bvx_mean_vfe": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_scatter_bev": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "bvx_profile_enable": (ctypes.c_int, [_vp, _i32]),
+    "bvx_profile_read": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64),
+                                        _i32]),
     "bvx_last_error": (ctypes.c_char_p, [_vp]),
     "bvx_launch_count": (ctypes.c_int64, []),
     "bvx_abi_version": (ctypes.c_int, []),

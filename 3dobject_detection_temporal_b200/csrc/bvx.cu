@@ -36,7 +36,9 @@ struct bvx_handle {
     int* slot = nullptr;
     unsigned int* cand = nullptr;
     unsigned int* first = nullptr;
-    int* wordrank = nullptr;
+    int* wordlocal = nullptr;
+    int* chunkbase = nullptr;
+    long long chunks_cap = 0;
     int* bucket = nullptr;
     int* cnt = nullptr;
     int2* ovf = nullptr;
@@ -51,6 +53,7 @@ struct bvx_handle {
     std::vector<FrameDesc> h_frames;
     std::vector<SegDesc> h_segs;
     std::vector<char> uploaded;  // byte image of the last uploaded layout
+    bool all_plain = false;      // every frame of the current layout is one plain segment
     static const int kRing = 4;
     char* pin[kRing] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t pin_ev[kRing];
@@ -69,7 +72,39 @@ struct bvx_handle {
     int* dev_offs = nullptr;
     size_t dev_out_voxels = 0;  // voxel capacity of the dev_* outputs
     int dev_out_tf = 0;
+    // optional per-kernel timing (bvx_profile_*): CUDA events around every launch
+    bool prof = false;
+    std::vector<cudaEvent_t> prof_pool;      // all events ever created
+    std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_pending;
+    size_t prof_used = 0;
+    double prof_ms[BVX_PROFILE_SLOTS] = {0};
+    long long prof_n[BVX_PROFILE_SLOTS] = {0};
     std::string err;
+};
+
+static cudaEvent_t prof_event(bvx_handle* h)
+{
+    if (h->prof_used == h->prof_pool.size()) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        h->prof_pool.push_back(e);
+    }
+    return h->prof_pool[h->prof_used++];
+}
+
+struct ProfScope {
+    bvx_handle* h;
+    int id;
+    cudaStream_t st;
+    cudaEvent_t a, b;
+    ProfScope(bvx_handle* h_, int id_, cudaStream_t st_) : h(h_), id(id_), st(st_), a(nullptr), b(nullptr)
+    {
+        if (h->prof) { a = prof_event(h); b = prof_event(h); cudaEventRecord(a, st); }
+    }
+    ~ProfScope()
+    {
+        if (h->prof) { cudaEventRecord(b, st); h->prof_pending.push_back({id, {a, b}}); }
+    }
 };
 
 static int fail(bvx_handle* h, int code, const char* fmt, ...)
@@ -148,7 +183,7 @@ extern "C" int bvx_destroy(bvx_handle* h)
     if (!h) return BVX_OK;
     cudaSetDevice(h->device);
     cudaFree(h->table); cudaFree(h->slot); cudaFree(h->cand); cudaFree(h->first);
-    cudaFree(h->wordrank); cudaFree(h->bucket); cudaFree(h->cnt); cudaFree(h->ovf);
+    cudaFree(h->wordlocal); cudaFree(h->chunkbase); cudaFree(h->bucket); cudaFree(h->cnt); cudaFree(h->ovf);
     cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
     cudaFree(h->d_offsets_scratch);
     cudaFree(h->dev_points); cudaFree(h->dev_voxels); cudaFree(h->dev_coors);
@@ -158,6 +193,7 @@ extern "C" int bvx_destroy(bvx_handle* h)
     }
     if (h->stage_in) cudaFreeHost(h->stage_in);
     if (h->stage_out) cudaFreeHost(h->stage_out);
+    for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
     delete h;
     return BVX_OK;
 }
@@ -219,7 +255,9 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if ((e = dalloc(h, &h->slot, (size_t)np)) != cudaSuccess) return bail(e, "alloc slot");
     if ((e = dalloc(h, &h->cand, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc cand");
     if ((e = dalloc(h, &h->first, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc first");
-    if ((e = dalloc(h, &h->wordrank, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc wordrank");
+    if ((e = dalloc(h, &h->wordlocal, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc wordlocal");
+    h->chunks_cap = np / kChunk + 2 * nf + 8;
+    if ((e = dalloc(h, &h->chunkbase, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkbase");
     if ((e = dalloc(h, &h->bucket, (size_t)h->voxel_cap * cfg->max_num_points)) != cudaSuccess) return bail(e, "alloc bucket");
     if ((e = dalloc(h, &h->cnt, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc cnt");
     if (cfg->max_num_points > kChainMaxT)
@@ -242,6 +280,7 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     }
     if ((e = cudaMemset(h->cnt, 0, (size_t)h->voxel_cap * 4)) != cudaSuccess) return bail(e, "memset cnt");
     if ((e = cudaMemset(h->counters, 0, 32)) != cudaSuccess) return bail(e, "memset counters");
+    if ((e = cudaMemset(h->d_state, 0, sizeof(FrameState) * (size_t)nf)) != cudaSuccess) return bail(e, "memset state");
     h->pin_bytes = sizeof(FrameDesc) * (size_t)nf + sizeof(SegDesc) * (size_t)h->seg_cap;
     for (int i = 0; i < bvx_handle::kRing; ++i) {
         if ((e = cudaMallocHost((void**)&h->pin[i], h->pin_bytes)) != cudaSuccess) return bail(e, "alloc pinned ring");
@@ -274,8 +313,9 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
     const int B = (int)frames.size();
     h->h_frames.assign(B, FrameDesc());
     h->h_segs.clear();
-    long long pt = 0, wd = 0, tb = 0;
+    long long pt = 0, wd = 0, tb = 0, ck = 0;
     int max_n = 0, max_words = 0;
+    bool all_plain = true;
     *all_aligned = true;
     for (int f = 0; f < B; ++f) {
         FrameDesc& fd = h->h_frames[f];
@@ -308,6 +348,14 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
         }
         if (n > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
         fd.n = (int)n;
+        fd.pts0 = nullptr;
+        if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform)
+            fd.pts0 = frames[f].sweeps[0].points;
+        else if (n > 0)
+            all_plain = false;
+        fd.chunk_off = (int)ck;
+        fd.nchunks = (int)((n + kChunk - 1) / kChunk);
+        ck += fd.nchunks;
         fd.pt_off = (int)pt;
         fd.word_off = (int)wd;
         fd.nwords = (int)((n + 31) / 32);
@@ -335,7 +383,8 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
         return fail(h, BVX_ERR_WORKSPACE, "%lld points exceed the handle capacity max_points=%d", pt, h->cfg.max_points);
     if (B > h->cfg.max_frames)
         return fail(h, BVX_ERR_WORKSPACE, "%d frames exceed the handle capacity max_frames=%d", B, h->cfg.max_frames);
-    if (tb > h->table_slots || wd > h->words_cap || (int)h->h_segs.size() > h->seg_cap)
+    h->all_plain = all_plain;
+    if (tb > h->table_slots || wd > h->words_cap || ck > h->chunks_cap || (int)h->h_segs.size() > h->seg_cap)
         return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, words %lld/%lld, segs %zu/%d)",
                     tb, h->table_slots, wd, h->words_cap, h->h_segs.size(), h->seg_cap);
     *max_n_out = max_n;
@@ -407,7 +456,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.slot = h->slot;
     p.cand = h->cand;
     p.first = h->first;
-    p.wordrank = h->wordrank;
+    p.wordlocal = h->wordlocal;
+    p.chunkbase = h->chunkbase;
     p.bucket = h->bucket;
     p.cnt = h->cnt;
     p.ovf = h->ovf;
@@ -429,33 +479,52 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.mean_c = o.mean_c;
 
     const int T = p.T;
-    const int chunks = (max_n + kBlock - 1) / kBlock;
-    const int wchunks = (max_words + kBlock - 1) / kBlock;
+    const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
+    (void)max_words;
     if (chunks > 0) {
+        ProfScope ps(h, 0, st);
         k_insert<<<dim3(chunks, B), kBlock, 0, st>>>(p);
-        k_verify<<<dim3(wchunks, B), kBlock, 0, st>>>(p);
-        g_launches += 2;
+        g_launches += 1;
     }
-    k_rank<<<B, kRankThreads, 0, st>>>(p);
-    g_launches += 1;
+    {   // always runs: an empty frame still needs its state and the offsets written
+        ProfScope ps(h, 1, st);
+        k_verify<<<dim3(std::max(chunks, 1), B), kBlock, 0, st>>>(p);
+        g_launches += 1;
+    }
     if (chunks > 0) {
-        k_slot<<<dim3(chunks, B), kBlock, 0, st>>>(p);
+        { ProfScope ps(h, 3, st); k_slot<<<dim3(chunks, B), kBlock, 0, st>>>(p); }
         g_launches += 1;
         if (T > kChainMaxT) {
             const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
+            ProfScope ps(h, 4, st);
             k_overflow<<<ob, kBlock, 0, st>>>(p);
             g_launches += 1;
         }
     }
-    const int vt = std::max(1, kBlock / T);
-    const int tiles = (cap + vt - 1) / vt;
-    const size_t smem = (size_t)((vt * T + 3) & ~3) * 4 + (size_t)vt * T * f_out * 4;
-    if (smem > 200 * 1024)
-        return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", smem);
-    if (smem > 48 * 1024)
-        CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_gather<<<dim3(tiles + wchunks, B), kBlock, smem, st>>>(p, tiles, vt);
-    g_launches += 1;
+    const bool small = T <= kChainMaxT && f_out == 4 && p.vec4 && h->all_plain;
+    if (small) {
+        const int tiles = (cap + kBlock - 1) / kBlock;
+        const size_t smem = (size_t)kWarps * 32 * T * 16;
+        const dim3 grid(tiles + chunks, B);
+        ProfScope ps(h, 5, st);
+        switch (T) {
+#define BVX_GS(TT) case TT: k_gather_small<TT><<<grid, kBlock, smem, st>>>(p, tiles); break;
+            BVX_GS(1) BVX_GS(2) BVX_GS(3) BVX_GS(4) BVX_GS(5) BVX_GS(6) BVX_GS(7) BVX_GS(8)
+#undef BVX_GS
+        }
+        g_launches += 1;
+    } else {
+        const int vt = std::max(1, kBlock / T);
+        const int tiles = (cap + vt - 1) / vt;
+        const size_t smem = (size_t)((vt * T + 3) & ~3) * 4 + (size_t)vt * T * f_out * 4;
+        if (smem > 200 * 1024)
+            return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", smem);
+        if (smem > 48 * 1024)
+            CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ProfScope ps(h, 5, st);
+        k_gather<<<dim3(tiles + chunks, B), kBlock, smem, st>>>(p, tiles, vt);
+        g_launches += 1;
+    }
     if (o.voxel_num) {
         CK(h, cudaMemcpyAsync(o.voxel_num, p.frame_voxel_offsets + B, 4, cudaMemcpyDeviceToDevice, st));
     }
@@ -646,6 +715,34 @@ extern "C" int bvx_generate_host(bvx_handle* h, const float* points, int32_t n, 
     const void* src[3] = {h->dev_voxels, h->dev_coors, h->dev_num};
     const size_t bytes[3] = {m * T * f * 4, m * 12, m * 4};
     return stage_out(h, dst, src, bytes, st);
+}
+
+// ------------------------------------------------------------------ profiling
+extern "C" int bvx_profile_enable(bvx_handle* h, int32_t on)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    h->prof = on != 0;
+    return BVX_OK;
+}
+
+extern "C" int bvx_profile_read(bvx_handle* h, double* ms, int64_t* launches, int32_t reset)
+{
+    if (!h || !ms || !launches) return fail(h, BVX_ERR_BAD_ARGUMENT, "null argument");
+    for (auto& pe : h->prof_pending) {
+        float t = 0.f;
+        CK(h, cudaEventSynchronize(pe.second.second));
+        CK(h, cudaEventElapsedTime(&t, pe.second.first, pe.second.second));
+        h->prof_ms[pe.first] += t;
+        h->prof_n[pe.first] += 1;
+    }
+    h->prof_pending.clear();
+    h->prof_used = 0;
+    for (int i = 0; i < BVX_PROFILE_SLOTS; ++i) {
+        ms[i] = h->prof_ms[i];
+        launches[i] = h->prof_n[i];
+        if (reset) { h->prof_ms[i] = 0; h->prof_n[i] = 0; }
+    }
+    return BVX_OK;
 }
 
 // ------------------------------------------------------------------ VFE / scatter

@@ -1,21 +1,25 @@
 // bvx_kernels.cuh -- sm_100a kernels of the voxelization hot path.
 //
 // Pipeline (one pass of VoxelGenerator.generate over B frames; DESIGN.md has the
-// data layout and the per-kernel roofline):
-//   k_insert  per point : cell key -> table slot, first occurrence by 64-bit
-//                         atomicMin/atomicCAS on {cell:32 | point index:32}
-//   k_verify  per cand. : candidate bit -> true first-occurrence bit, word popcounts
-//   k_rank    per frame : exclusive scan of the popcounts -> first-come voxel
-//                         ranks, M = min(total, cap), break cut-off index i*
-//   k_slot    per point : voxel id from the first-occurrence rank; deterministic
-//                         slot in input order (sorted atomicMin chain, or
-//                         count + bucket for large T)
-//   k_overflow          : (large T only) T-smallest selection for crowded voxels
-//   k_gather  per voxel : shared-memory staged row gather, zero padding,
-//                         num_points, optional fused mean VFE; the extra blocks
-//                         of the same launch reset the touched table entries
-// Everything is fp32 / int32; there is no contraction anywhere, hence no tensor
-// cores: the bound is HBM / L2 bandwidth.
+// data layout and the per-kernel roofline).  Work is cut into chunks of 1024
+// consecutive points (256 threads x 4 points, all four loads in flight at once):
+//   k_insert  per chunk : cell key -> table slot; first occurrence by 64-bit
+//                         atomicCAS/atomicMin on {cell:32 | point index:32};
+//                         candidate bit per point ("held the minimum when I left")
+//   k_verify  per chunk : candidate -> true first-occurrence bits, per-word and
+//                         per-chunk counts; the LAST chunk of a frame scans the
+//                         chunk counts (first-come voxel ranks, M = min(total,
+//                         cap), break cut-off i*), the last frame prefix-sums M
+//   k_slot    per chunk : voxel id = rank of the voxel's first point; slot inside
+//                         the voxel in input order (sorted atomicMin chain for
+//                         T <= 8, count + bucket for larger T)
+//   k_overflow          : (T > 8) T-smallest selection for crowded voxels
+//   k_gather  per voxel : rows -> voxels (zero padded), coordinates from the first
+//                         point, num_points, optional fused mean VFE; extra blocks
+//                         of the same launch reset the table entries the frame
+//                         touched, so the next call needs no memset
+// Everything is fp32 / int32; nothing here is a contraction, hence no tensor
+// cores: the bounds are HBM bandwidth and L2 random-access / atomic throughput.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -24,9 +28,12 @@ namespace bvx {
 
 constexpr unsigned long long kEmpty64 = 0xFFFFFFFFFFFFFFFFull;
 constexpr int kEmptyIdx = 0x7FFFFFFF;
-constexpr int kChainMaxT = 8;      // T <= 8: sorted atomicMin chain; else count+bucket
+constexpr int kChainMaxT = 8;        // T <= 8: sorted atomicMin chain; else count+bucket
 constexpr int kBlock = 256;
-constexpr int kRankThreads = 1024;
+constexpr int kPts = 4;              // points per thread
+constexpr int kChunk = kBlock * kPts;  // 1024 points per chunk
+constexpr int kChunkWords = kChunk / 32;
+constexpr int kWarps = kBlock / 32;
 
 struct GridParams {
     float lo[3];
@@ -36,13 +43,16 @@ struct GridParams {
 };
 
 struct FrameDesc {
+    const float* pts0;           // points of the frame when it is ONE plain segment, else null
     unsigned long long tbl_off;  // entry offset of this frame's table region
     unsigned int tbl_mask;       // slots - 1 (hashed)
     int tbl_shift;               // 32 - log2(slots) (hashed); -1 => dense (slot = cell)
     int n;                       // points in the frame (all segments)
     int pt_off;                  // base into slot[]
-    int word_off;                // base into cand/first/wordrank
+    int word_off;                // base into cand/first/wordlocal
     int nwords;
+    int chunk_off;               // base into chunkbase[]
+    int nchunks;
     int seg_begin;
     int seg_count;
 };
@@ -59,10 +69,10 @@ struct SegDesc {
 };
 
 struct FrameState {
-    int total;   // distinct in-range cells
-    int m;       // voxels kept = min(total, cap)
-    int istar;   // break cut-off: points with index >= istar are dropped
-    int pad;
+    int total;        // distinct in-range cells
+    int m;            // voxels kept = min(total, cap)
+    int istar;        // break cut-off: points with index >= istar are dropped
+    int done_verify;  // chunks of k_verify finished (last-block detection); reset by the scanner
 };
 
 struct Pipe {
@@ -74,7 +84,8 @@ struct Pipe {
     int* slot;
     unsigned int* cand;
     unsigned int* first;
-    int* wordrank;
+    int* wordlocal;      // exclusive prefix of first-occurrence counts inside the word's chunk
+    int* chunkbase;      // per chunk: count, then exclusive prefix over the frame's chunks
     int* bucket;
     int* cnt;
     int2* ovf;
@@ -134,164 +145,208 @@ __device__ __forceinline__ unsigned int hash_cell(unsigned int cell, int shift)
     return (cell * 0x9E3779B1u) >> shift;
 }
 
+// xyz of frame-local point i (sweep transform applied)
+__device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int i, float& x, float& y,
+                                         float& z)
+{
+    if (fr.pts0) {
+        if (p.vec4) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(fr.pts0) + i);  // streamed once
+            x = v.x; y = v.y; z = v.z;
+        } else {
+            const float* q = fr.pts0 + (size_t)i * p.f_in;
+            x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
+        }
+        return;
+    }
+    const SegDesc& sg = find_seg(p, fr, i);
+    const float* q = sg.pts + (size_t)(i - sg.start) * p.f_in;
+    if (p.vec4) {
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(q));
+        x = v.x; y = v.y; z = v.z;
+    } else {
+        x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
+    }
+    xform(sg, x, y, z);
+}
+
+// full output row (f_out floats) of frame-local point i
+__device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, int i, float* dst)
+{
+    const float* q;
+    const SegDesc* sg = nullptr;
+    if (fr.pts0) {
+        q = fr.pts0 + (size_t)i * p.f_in;
+    } else {
+        sg = &find_seg(p, fr, i);
+        q = sg->pts + (size_t)(i - sg->start) * p.f_in;
+    }
+    float x, y, z;
+    if (p.vec4) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(q));
+        x = v.x; y = v.y; z = v.z;
+        dst[3] = v.w;
+    } else {
+        x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
+        for (int k = 3; k < p.f_in; ++k) dst[k] = __ldg(q + k);
+    }
+    if (sg) {
+        xform(*sg, x, y, z);
+        if (sg->has_dt) dst[p.f_in] = sg->dt;
+    }
+    dst[0] = x; dst[1] = y; dst[2] = z;
+}
+
 // ---------------------------------------------------------------- k_insert
-// grid (ceil(max_n / kBlock), B); one point per thread; a warp covers one
-// 32-point mask word.
+// grid (max chunks per frame, B).  Thread t of chunk c owns points
+// c*1024 + k*256 + t, k = 0..3: every warp-wide access is coalesced and a warp
+// covers exactly one 32-point mask word per k.
 __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
 {
     const FrameDesc fr = p.frames[blockIdx.y];
-    const int i = blockIdx.x * kBlock + threadIdx.x;
-    if (blockIdx.x * kBlock >= fr.n) return;
-    bool won = false;
-    int myslot = -1;
-    if (i < fr.n) {
-        const SegDesc& sg = find_seg(p, fr, i);
-        const float* q = sg.pts + (size_t)(i - sg.start) * p.f_in;
-        float x, y, z;
-        if (p.vec4) {
-            const float4 v = __ldg(reinterpret_cast<const float4*>(q));
-            x = v.x; y = v.y; z = v.z;
-        } else {
-            x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
+    const int base = blockIdx.x * kChunk;
+    if (base >= fr.n) return;
+    unsigned long long* tbl = p.table + fr.tbl_off;
+    int cell[kPts];
+    unsigned int h[kPts];
+    unsigned long long e[kPts];
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        cell[k] = -1;
+        if (i < fr.n) {
+            float x, y, z;
+            load_xyz(p, fr, i, x, y, z);
+            cell[k] = cell_of(p.g, x, y, z);
         }
-        xform(sg, x, y, z);
-        const int cell = cell_of(p.g, x, y, z);
-        if (cell >= 0) {
-            unsigned long long* tbl = p.table + fr.tbl_off;
-            unsigned int h = fr.tbl_shift < 0 ? (unsigned)cell : hash_cell((unsigned)cell, fr.tbl_shift);
-            const unsigned long long mine = ((unsigned long long)(unsigned)cell << 32) | (unsigned)i;
+    }
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        h[k] = 0; e[k] = 0;
+        if (cell[k] >= 0) {
+            h[k] = fr.tbl_shift < 0 ? (unsigned)cell[k] : hash_cell((unsigned)cell[k], fr.tbl_shift);
+            e[k] = __ldcg(tbl + h[k]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        bool won = false;
+        if (cell[k] >= 0) {
+            const unsigned int c = (unsigned)cell[k];
+            const unsigned long long mine = ((unsigned long long)c << 32) | (unsigned)i;
+            unsigned int hh = h[k];
+            unsigned long long ee = e[k];
             while (true) {
-                unsigned long long e = __ldcg(tbl + h);
-                bool done = false;
-                while (true) {
-                    if ((unsigned)(e >> 32) == (unsigned)cell) {
-                        if ((unsigned)e > (unsigned)i) {
-                            const unsigned long long old = atomicMin(tbl + h, mine);
-                            won = (unsigned)old > (unsigned)i;
-                        }
-                        done = true;
-                        break;
-                    }
-                    if (e == kEmpty64) {
-                        const unsigned long long old = atomicCAS(tbl + h, kEmpty64, mine);
-                        if (old == kEmpty64) { won = true; done = true; break; }
-                        e = old;
-                        continue;
+                if ((unsigned)(ee >> 32) == c) {              // my cell already has an entry
+                    if ((unsigned)ee > (unsigned)i) {
+                        const unsigned long long old = atomicMin(tbl + hh, mine);
+                        won = (unsigned)old > (unsigned)i;
                     }
                     break;
                 }
-                if (done) break;
-                h = (h + 1) & fr.tbl_mask;
+                if (ee == kEmpty64) {                         // claim the empty slot
+                    const unsigned long long old = atomicCAS(tbl + hh, kEmpty64, mine);
+                    if (old == kEmpty64) { won = true; break; }
+                    ee = old;                                 // lost the race: re-examine this slot
+                    continue;
+                }
+                hh = (hh + 1) & fr.tbl_mask;                  // other cell: linear probe
+                ee = __ldcg(tbl + hh);
             }
-            myslot = (int)h;
+            h[k] = hh;
         }
-        p.slot[fr.pt_off + i] = myslot;
+        if (i < fr.n) p.slot[fr.pt_off + i] = cell[k] >= 0 ? (int)h[k] : -1;
+        const unsigned int b = __ballot_sync(0xffffffffu, won);
+        const int w = i >> 5;
+        if ((threadIdx.x & 31) == 0 && w < fr.nwords) p.cand[fr.word_off + w] = b;
     }
-    const unsigned int b = __ballot_sync(0xffffffffu, won);
-    if ((threadIdx.x & 31) == 0 && (i >> 5) < fr.nwords) p.cand[fr.word_off + (i >> 5)] = b;
 }
 
 // ---------------------------------------------------------------- k_verify
-// grid (ceil(max_words / kBlock), B); one mask word per thread.
-__global__ void __launch_bounds__(kBlock) k_verify(const Pipe p)
+__device__ __forceinline__ int warp_exclusive_scan(int v, int lane, int* total)
 {
-    const FrameDesc fr = p.frames[blockIdx.y];
-    const int w = blockIdx.x * kBlock + threadIdx.x;
-    if (w >= fr.nwords) return;
-    unsigned int m = p.cand[fr.word_off + w];
-    unsigned int out = 0;
-    const unsigned long long* tbl = p.table + fr.tbl_off;
-    while (m) {
-        const int b = __ffs(m) - 1;
-        m &= m - 1;
-        const int i = w * 32 + b;
-        const int s = p.slot[fr.pt_off + i];
-        const unsigned long long e = __ldcg(tbl + s);
-        if ((unsigned)e == (unsigned)i) out |= 1u << b;
-    }
-    p.first[fr.word_off + w] = out;
-    p.wordrank[fr.word_off + w] = __popc(out);
-}
-
-// ---------------------------------------------------------------- k_rank
-__device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem /*[32]*/)
-{
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int inc = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, inc, d);
         if (lane >= d) inc += t;
     }
-    if (lane == 31) smem[wid] = inc;
-    __syncthreads();
-    if (wid == 0) {
-        int s = lane < (blockDim.x >> 5) ? smem[lane] : 0;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, s, d);
-            if (lane >= d) s += t;
-        }
-        smem[lane] = s;  // inclusive over warps
-    }
-    __syncthreads();
-    const int base = wid ? smem[wid - 1] : 0;
-    *total = smem[(blockDim.x >> 5) - 1];
-    __syncthreads();
-    return base + inc - v;
+    *total = __shfl_sync(0xffffffffu, inc, 31);
+    return inc - v;
 }
 
-// One block per frame.  Scans the per-word first-occurrence counts in place
-// (wordrank becomes the exclusive prefix), derives M and the break cut-off; the
-// last block to finish prefix-sums M over the frames of the call.
-__global__ void __launch_bounds__(kRankThreads) k_rank(const Pipe p)
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem /*[kWarps+1]*/)
 {
-    __shared__ int sm[32];
-    __shared__ int s_last;
-    const int f = blockIdx.x;
-    const FrameDesc fr = p.frames[f];
-    int* wr = p.wordrank + fr.word_off;
-    const unsigned int* fm = p.first + fr.word_off;
-    const int per = (fr.nwords + kRankThreads - 1) / kRankThreads;
-    const int w0 = min(threadIdx.x * per, fr.nwords), w1 = min(w0 + per, fr.nwords);
-    int local = 0;
-    for (int w = w0; w < w1; ++w) local += wr[w];
-    int total;
-    const int excl = block_exclusive_scan(local, &total, sm);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int wt;
+    const int ex = warp_exclusive_scan(v, lane, &wt);
+    __syncthreads();
+    if (lane == 31) smem[wid] = wt;
+    __syncthreads();
+    int base = 0, tot = 0;
+#pragma unroll
+    for (int k = 0; k < kWarps; ++k) {
+        const int s = smem[k];
+        if (k < wid) base += s;
+        tot += s;
+    }
+    *total = tot;
+    return base + ex;
+}
+
+// Frame-level part, run by the last chunk of the frame to finish k_verify: scan the
+// chunk counts in place (chunkbase becomes the exclusive prefix), publish total / M /
+// i*, and -- for the last frame of the call -- the exclusive prefix of M over frames.
+__device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int* sm)
+{
+    int* cb = p.chunkbase + fr.chunk_off;
     const int cap = p.cap;
+    int carry = 0;
+    int cut_chunk = -1, cut_base = 0;
+    for (int b0 = 0; b0 < fr.nchunks; b0 += kBlock) {
+        const int c = b0 + threadIdx.x;
+        const int v = c < fr.nchunks ? __ldcg(cb + c) : 0;
+        int tot;
+        const int ex = carry + block_exclusive_scan(v, &tot, sm);
+        if (c < fr.nchunks) {
+            cb[c] = ex;
+            if (ex <= cap && cap < ex + v) { cut_chunk = c; cut_base = ex; }  // at most one thread
+        }
+        carry += tot;
+    }
+    const int total = carry;
     const bool cut = (!p.overflow_continue) && total > cap;
     if (threadIdx.x == 0) {
-        FrameState st;
-        st.total = total;
-        st.m = min(total, cap);
-        st.istar = fr.n;  // overwritten below by the owner of the cut word
-        st.pad = 0;
-        p.state[f] = st;
+        p.state[f].total = total;
+        p.state[f].m = min(total, cap);
+        p.state[f].done_verify = 0;            // ready for the next call
+        if (!cut) p.state[f].istar = fr.n;
     }
-    __syncthreads();
-    int run = excl;
-    for (int w = w0; w < w1; ++w) {
-        const int c = wr[w];
-        wr[w] = run;
-        if (cut && run <= cap && cap < run + c) {
-            // (cap - run)-th set bit (0-based) of first[w] is the point that would open voxel #cap
-            unsigned int m = fm[w];
-            for (int k = cap - run; k > 0; --k) m &= m - 1;
-            p.state[f].istar = w * 32 + (__ffs(m) - 1);
-        }
-        run += c;
+    if (cut && cut_chunk >= 0) {
+        // the point that would open voxel #cap: (cap - prefix)-th first occurrence of this chunk
+        int need = cap - cut_base;
+        const int w0 = fr.word_off + cut_chunk * kChunkWords;
+        const int nw = min(kChunkWords, fr.nwords - cut_chunk * kChunkWords);
+        int w = 0;
+        for (; w + 1 < nw; ++w)
+            if (__ldcg(p.wordlocal + w0 + w + 1) > need) break;
+        need -= __ldcg(p.wordlocal + w0 + w);
+        unsigned int m = __ldcg(p.first + w0 + w);
+        for (; need > 0; --need) m &= m - 1;
+        p.state[f].istar = (cut_chunk * kChunkWords + w) * 32 + (__ffs(m) - 1);
     }
-    // ---- last block: exclusive prefix of M over frames
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) s_last = (atomicAdd(&p.counters[0], 1) == p.nframes - 1);
+    __shared__ int s_lastframe;
+    if (threadIdx.x == 0) s_lastframe = (atomicAdd(&p.counters[0], 1) == p.nframes - 1);
     __syncthreads();
-    if (!s_last) return;
+    if (!s_lastframe) return;
     __threadfence();
-    int carry = 0;
-    for (int base = 0; base < p.nframes; base += kRankThreads) {
-        const int ff = base + threadIdx.x;
-        const int m = ff < p.nframes ? ((volatile FrameState*)p.state)[ff].m : 0;
+    carry = 0;
+    for (int b0 = 0; b0 < p.nframes; b0 += kBlock) {
+        const int ff = b0 + threadIdx.x;
+        const int m = ff < p.nframes ? __ldcg(&p.state[ff].m) : 0;
         int tot;
         const int ex = block_exclusive_scan(m, &tot, sm);
         if (ff < p.nframes) p.frame_voxel_offsets[ff] = carry + ex;
@@ -304,49 +359,117 @@ __global__ void __launch_bounds__(kRankThreads) k_rank(const Pipe p)
     }
 }
 
+// grid (max chunks per frame, B); same point mapping as k_insert.
+__global__ void __launch_bounds__(kBlock) k_verify(const Pipe p)
+{
+    __shared__ unsigned int s_first[kChunkWords];
+    __shared__ int sm[kWarps + 1];
+    __shared__ int s_last;
+    const int f = blockIdx.y;
+    const FrameDesc fr = p.frames[f];
+    const int base = blockIdx.x * kChunk;
+    if (base >= fr.n && !(fr.n == 0 && blockIdx.x == 0)) return;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned long long* tbl = p.table + fr.tbl_off;
+    if (fr.n > 0) {
+        int sl[kPts];
+        bool cd[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const int i = base + k * kBlock + threadIdx.x;
+            const int w = i >> 5;
+            const unsigned int cw = w < fr.nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
+            cd[k] = (cw >> lane) & 1u;
+            sl[k] = cd[k] ? __ldg(p.slot + fr.pt_off + i) : 0;
+        }
+        unsigned long long e[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) e[k] = cd[k] ? __ldcg(tbl + sl[k]) : 0ull;
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const int i = base + k * kBlock + threadIdx.x;
+            const bool isf = cd[k] && (unsigned)e[k] == (unsigned)i;
+            const unsigned int b = __ballot_sync(0xffffffffu, isf);
+            if (lane == 0) s_first[k * kWarps + wid] = b;
+        }
+        __syncthreads();
+        if (wid == 0) {
+            const unsigned int fw = s_first[lane];
+            int tot;
+            const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
+            const int w = blockIdx.x * kChunkWords + lane;
+            if (w < fr.nwords) {
+                p.first[fr.word_off + w] = fw;
+                p.wordlocal[fr.word_off + w] = ex;
+            }
+            if (lane == 0) p.chunkbase[fr.chunk_off + blockIdx.x] = tot;
+        }
+    }
+    // last chunk of the frame -> frame-level scan
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        s_last = (atomicAdd(&p.state[f].done_verify, 1) == max(fr.nchunks, 1) - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    frame_scan(p, fr, f, sm);
+}
+
 // ---------------------------------------------------------------- k_slot
-// grid (ceil(max_n / kBlock), B); one point per thread.
+// grid (max chunks per frame, B).  Chunks at or beyond the break cut-off exit at once.
 __global__ void __launch_bounds__(kBlock) k_slot(const Pipe p)
 {
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
-    const FrameState st = p.state[f];
-    const int i = blockIdx.x * kBlock + threadIdx.x;
-    if (i >= fr.n || i >= st.istar) return;
-    const int s = p.slot[fr.pt_off + i];
-    if (s < 0) return;
-    const unsigned long long e = __ldcg(p.table + fr.tbl_off + s);
-    const unsigned int fidx = (unsigned)e;
-    const int w = fidx >> 5;
-    const int rank = p.wordrank[fr.word_off + w] +
-                     __popc(p.first[fr.word_off + w] & ((1u << (fidx & 31)) - 1u));
-    if (rank >= p.cap) return;  // continue mode: voxel beyond the cap
-    const size_t g = (size_t)f * p.cap + rank;
-    if (fidx == (unsigned)i) {
-        const int cell = (int)(e >> 32);
-        const int gx = p.g.gs[0], gy = p.g.gs[1];
-        const int x = cell % gx, r = cell / gx;
-        const int y = r % gy, z = r / gy;
-        int* c = p.coors + (size_t)(p.frame_voxel_offsets[f] + rank) * p.coor_cols;
-        if (p.coor_cols == 4) { *reinterpret_cast<int4*>(c) = make_int4(f, z, y, x); }
-        else { c[0] = z; c[1] = y; c[2] = x; }
+    const int base = blockIdx.x * kChunk;
+    if (base >= fr.n) return;
+    const int istar = p.state[f].istar;
+    if (base >= istar) return;
+    const unsigned long long* tbl = p.table + fr.tbl_off;
+    int sl[kPts];
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        sl[k] = (i < fr.n && i < istar) ? __ldg(p.slot + fr.pt_off + i) : -1;
     }
-    int* b = p.bucket + g * p.T;
-    if (p.T <= kChainMaxT) {
-        // sorted insertion: slot k ends up holding the (k+1)-th smallest index offered
-        int cur = i;
-        for (int k = 0; k < p.T; ++k) {
-            const int old = atomicMin(b + k, cur);
-            if (old == kEmptyIdx) break;
-            cur = max(old, cur);
+    unsigned long long e[kPts];
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) e[k] = sl[k] >= 0 ? __ldcg(tbl + sl[k]) : 0ull;
+    int rank[kPts];
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        rank[k] = 0x7FFFFFFF;
+        if (sl[k] >= 0) {
+            const unsigned int fidx = (unsigned)e[k];
+            const int w = fidx >> 5;
+            rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
+                      __ldg(p.wordlocal + fr.word_off + w) +
+                      __popc(__ldg(p.first + fr.word_off + w) & ((1u << (fidx & 31)) - 1u));
         }
-    } else {
-        const int c = atomicAdd(p.cnt + g, 1);
-        if (c < p.T) {
-            b[c] = i;
+    }
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        if (rank[k] >= p.cap) continue;   // out of range, cut off, or (continue mode) beyond the cap
+        const int i = base + k * kBlock + threadIdx.x;
+        const size_t g = (size_t)f * p.cap + rank[k];
+        int* b = p.bucket + g * p.T;
+        if (p.T <= kChainMaxT) {
+            // sorted insertion: slot j ends up holding the (j+1)-th smallest index offered
+            int cur = i;
+            for (int j = 0; j < p.T; ++j) {
+                const int old = atomicMin(b + j, cur);
+                if (old == kEmptyIdx) break;
+                cur = max(old, cur);
+            }
         } else {
-            const int o = atomicAdd(&p.counters[1], 1);
-            if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
+            const int c = atomicAdd(p.cnt + g, 1);
+            if (c < p.T) {
+                b[c] = i;
+            } else {
+                const int o = atomicAdd(&p.counters[1], 1);
+                if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
+            }
         }
     }
 }
@@ -372,46 +495,123 @@ __global__ void __launch_bounds__(kBlock) k_overflow(const Pipe p)
 }
 
 // ---------------------------------------------------------------- k_gather
-__device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, int i, float* dst)
+// Table reset, shared by both gather kernels: blocks past the voxel tiles walk the
+// frame's chunks and clear the slot of every candidate (a superset of the entries
+// the frame created), so the next call starts from an empty table without a memset.
+__device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, int chunk)
 {
-    const SegDesc& sg = find_seg(p, fr, i);
-    const float* q = sg.pts + (size_t)(i - sg.start) * p.f_in;
-    float x, y, z;
-    if (p.vec4) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(q));
-        x = v.x; y = v.y; z = v.z;
-        dst[3] = v.w;
-    } else {
-        x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
-        for (int k = 3; k < p.f_in; ++k) dst[k] = __ldg(q + k);
+    const int base = chunk * kChunk;
+    if (base >= fr.n) return;
+    const int lane = threadIdx.x & 31;
+    unsigned long long* tbl = p.table + fr.tbl_off;
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        const int w = i >> 5;
+        const unsigned int cw = w < fr.nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
+        if ((cw >> lane) & 1u) tbl[__ldg(p.slot + fr.pt_off + i)] = kEmpty64;
     }
-    xform(sg, x, y, z);
-    dst[0] = x; dst[1] = y; dst[2] = z;
-    if (sg.has_dt) dst[p.f_in] = sg.dt;
 }
 
-// grid (tiles + reset_blocks, B).  Blocks [0, tiles): a tile of vt voxels (vt*T
-// bucket entries) staged through shared memory.  Blocks [tiles, ...): reset the
-// table entries the frame touched (every candidate's slot), so the next call
-// starts from an empty table without a memset.
-// dynamic smem: round4(E) ints + E*f_out floats, E = vt*T.
+__device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int cell)
+{
+    const int gx = p.g.gs[0], gy = p.g.gs[1];
+    const int x = cell % gx, r = cell / gx;
+    const int y = r % gy, z = r / gy;
+    if (p.coor_cols == 4) {
+        reinterpret_cast<int4*>(p.coors)[gv] = make_int4(f, z, y, x);
+    } else {
+        int* c = p.coors + gv * 3;
+        c[0] = z; c[1] = y; c[2] = x;
+    }
+}
+
+// Fast path: T <= 8 (bucket already sorted by the atomicMin chain), 4 floats per
+// point, 16-byte aligned rows.  One thread per voxel: T independent row loads in
+// flight, mean and coordinates from registers; the voxel rows go through a
+// per-warp shared-memory transpose so the [M, T, 4] store is fully coalesced.
+// grid (tiles + reset chunks, B); dynamic smem = kWarps * 32 * T * 16 bytes.
+template <int T>
+__global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles)
+{
+    extern __shared__ float4 smem_v[];
+    const int f = blockIdx.y;
+    const FrameDesc fr = p.frames[f];
+    if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
+    const int mf = p.state[f].m;
+    const int v0 = blockIdx.x * kBlock;
+    if (v0 >= mf) return;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int v = v0 + threadIdx.x;
+    const bool live = v < mf;
+    const size_t gbase = (size_t)p.frame_voxel_offsets[f];
+    int idx[T];
+    int* gb = p.bucket + ((size_t)f * p.cap + v) * T;
+#pragma unroll
+    for (int s = 0; s < T; ++s) {
+        idx[s] = live ? gb[s] : kEmptyIdx;
+        if (live) gb[s] = kEmptyIdx;
+    }
+    float4 row[T];
+    int nvalid = 0;
+#pragma unroll
+    for (int s = 0; s < T; ++s) {
+        row[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (idx[s] != kEmptyIdx) {
+            row[s] = __ldg(reinterpret_cast<const float4*>(fr.pts0) + idx[s]);
+            ++nvalid;
+        }
+    }
+    // per-warp transpose: voxel-major float4 index lane*T + s, read back linearly
+    float4* sw = smem_v + wid * (32 * T);
+#pragma unroll
+    for (int s = 0; s < T; ++s) {
+        int q = lane * T + s;
+        if ((T & 1) == 0) q ^= (q >> 3) & 7;
+        sw[q] = row[s];
+    }
+    __syncwarp();
+    const int wv0 = v0 + wid * 32;                    // first voxel of this warp
+    const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
+    float4* out = reinterpret_cast<float4*>(p.voxels) + (gbase + wv0) * T;
+#pragma unroll
+    for (int s = 0; s < T; ++s) {
+        const int j = s * 32 + lane;
+        int q = j;
+        if ((T & 1) == 0) q ^= (q >> 3) & 7;
+        if (j < wn * T) __stcs(out + j, sw[q]);
+    }
+    if (!live) return;
+    const size_t gv = gbase + v;
+    p.num_points[gv] = nvalid;
+    write_coor(p, f, gv, cell_of(p.g, row[0].x, row[0].y, row[0].z));
+    if (p.mean_out) {
+        float sx = 0.f, sy = 0.f, sz = 0.f, swt = 0.f;
+#pragma unroll
+        for (int s = 0; s < T; ++s) {
+            sx = __fadd_rn(sx, row[s].x); sy = __fadd_rn(sy, row[s].y);
+            sz = __fadd_rn(sz, row[s].z); swt = __fadd_rn(swt, row[s].w);
+        }
+        const float nf = (float)nvalid;
+        const float m4[4] = {__fdiv_rn(sx, nf), __fdiv_rn(sy, nf), __fdiv_rn(sz, nf), __fdiv_rn(swt, nf)};
+        if (p.mean_c == 4) {
+            reinterpret_cast<float4*>(p.mean_out)[gv] = make_float4(m4[0], m4[1], m4[2], m4[3]);
+        } else {
+            for (int c = 0; c < p.mean_c; ++c) p.mean_out[gv * p.mean_c + c] = m4[c];
+        }
+    }
+}
+
+// General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T bucket
+// entries) staged through shared memory; entries are rank-sorted in shared memory
+// (the large-T bucket is unordered).
+// grid (tiles + reset chunks, B); dynamic smem: round4(E) ints + E*f_out floats, E = vt*T.
 __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int vt)
 {
     extern __shared__ int smem_i[];
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
-    if ((int)blockIdx.x >= tiles) {
-        const int w = (blockIdx.x - tiles) * kBlock + threadIdx.x;
-        if (w >= fr.nwords) return;
-        unsigned int m = p.cand[fr.word_off + w];
-        unsigned long long* tbl = p.table + fr.tbl_off;
-        while (m) {
-            const int b = __ffs(m) - 1;
-            m &= m - 1;
-            tbl[p.slot[fr.pt_off + w * 32 + b]] = kEmpty64;
-        }
-        return;
-    }
+    if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * vt;
     if (v0 >= mf) return;
@@ -439,7 +639,11 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
             nvalid += (o != kEmptyIdx);
             r += (o < my);
         }
-        if (my != kEmptyIdx) fetch_row(p, fr, my, srow + (size_t)(v * T + r) * F);
+        if (my != kEmptyIdx) {
+            float* dst = srow + (size_t)(v * T + r) * F;
+            fetch_row(p, fr, my, dst);
+            if (r == 0) write_coor(p, f, gout + v, cell_of(p.g, dst[0], dst[1], dst[2]));
+        }
         if (s >= nvalid) {
             float* z = srow + (size_t)(v * T + s) * F;
             for (int k = 0; k < F; ++k) z[k] = 0.0f;
@@ -452,7 +656,7 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
     if ((tot & 3) == 0 && ((((size_t)gout * T * F) & 3) == 0)) {
         float4* o4 = reinterpret_cast<float4*>(out);
         const float4* s4 = reinterpret_cast<const float4*>(srow);
-        for (int k = threadIdx.x; k < (tot >> 2); k += kBlock) o4[k] = s4[k];
+        for (int k = threadIdx.x; k < (tot >> 2); k += kBlock) __stcs(o4 + k, s4[k]);
     } else {
         for (int k = threadIdx.x; k < tot; k += kBlock) out[k] = srow[k];
     }

@@ -142,6 +142,20 @@ class VoxelGenerator:
         _lib.check(_lib.load().bvx_workspace_bytes(self._handle, ctypes.byref(out)), self._handle)
         return int(out.value)
 
+    def profile(self, on=True):
+        """Per-kernel device timing (CUDA events around every launch) on/off."""
+        if self._handle is None:
+            raise RuntimeError("profile() needs a live handle: call generate once first")
+        _lib.check(_lib.load().bvx_profile_enable(self._handle, 1 if on else 0), self._handle)
+
+    def profile_read(self, reset=True):
+        """{kernel: (total_ms, launches)} accumulated since the last reset."""
+        ms = (ctypes.c_double * _lib.PROFILE_SLOTS)()
+        n = (ctypes.c_int64 * _lib.PROFILE_SLOTS)()
+        _lib.check(_lib.load().bvx_profile_read(self._handle, ms, n, 1 if reset else 0), self._handle)
+        return {_lib.KERNEL_NAMES[i]: (float(ms[i]), int(n[i])) for i in range(_lib.PROFILE_SLOTS)
+                if _lib.KERNEL_NAMES[i] and n[i] > 0}
+
     # ---- VoxelGenerator.generate
     def generate(self, points, max_voxels=None):
         """(voxels, coordinates, num_points_per_voxel) of one frame."""
@@ -252,7 +266,7 @@ class VoxelGenerator:
 
     # ---- B frames per call (+ the voxel part of merge_second_batch)
     def generate_batched(self, points, frame_offsets=None, max_voxels=None, mean_channels=0,
-                         padded=False):
+                         padded=False, out=None):
         """Voxelize B frames in one call.
 
         ``points``: list of per-frame arrays, or one [sum N, F] array/tensor with
@@ -260,7 +274,9 @@ class VoxelGenerator:
         (b,z,y,x), num_points[sumM], frame_voxel_offsets[B+1])`` (+ mean features
         [sumM, mean_channels] when ``mean_channels > 0``: the mean VFE fused into the
         gather kernel).  ``padded=True`` (device form) skips the host sync and returns
-        capacity-sized buffers.
+        capacity-sized buffers.  ``out`` = previously returned capacity-sized buffers
+        ``(voxels, coors, num, offsets[, mean])`` to write into instead of allocating
+        (CUDA tensors for the device form, ideally pinned numpy arrays for the host form).
         """
         max_voxels = int(max_voxels or self._max_voxels)
         if isinstance(points, (list, tuple)):
@@ -294,12 +310,20 @@ class VoxelGenerator:
             h = self._ensure(n, b, max_voxels, f, dev.index)
             cap = b * max_voxels
             with torch.cuda.device(dev):
-                voxels = torch.empty((cap, t, f), dtype=torch.float32, device=dev)
-                coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
-                num = torch.empty((cap,), dtype=torch.int32, device=dev)
-                fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
-                mean = (torch.empty((cap, mean_channels), dtype=torch.float32, device=dev)
-                        if mean_channels > 0 else None)
+                if out is not None:
+                    voxels, coors, num, fvo = out[:4]
+                    mean = out[4] if mean_channels > 0 else None
+                    if (tuple(voxels.shape) != (cap, t, f) or tuple(coors.shape) != (cap, 4)
+                            or num.shape[0] != cap or fvo.shape[0] != b + 1
+                            or (mean is not None and tuple(mean.shape) != (cap, mean_channels))):
+                        raise ValueError("out= buffers do not match this call's capacity shapes")
+                else:
+                    voxels = torch.empty((cap, t, f), dtype=torch.float32, device=dev)
+                    coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
+                    num = torch.empty((cap,), dtype=torch.int32, device=dev)
+                    fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
+                    mean = (torch.empty((cap, mean_channels), dtype=torch.float32, device=dev)
+                            if mean_channels > 0 else None)
                 st = torch.cuda.current_stream(dev).cuda_stream
                 _lib.check(lib.bvx_generate_batched(
                     h, points.data_ptr(), offs_p, b, f, max_voxels, voxels.data_ptr(), coors.data_ptr(),
@@ -311,16 +335,24 @@ class VoxelGenerator:
             return (voxels[:m], coors[:m], num[:m], fvo) + ((mean[:m],) if mean is not None else ())
         if mean_channels:
             raise ValueError("mean_channels is only available in the device form")
-        pts = np.ascontiguousarray(points, dtype=np.float32)
+        pts = points if (isinstance(points, np.ndarray) and points.dtype == np.float32
+                         and points.flags.c_contiguous) else np.ascontiguousarray(points, dtype=np.float32)
         n, f = pts.shape
         if int(offs[-1]) != n:
             raise ValueError("frame_offsets[-1] must equal the number of points")
         h = self._ensure(n, b, max_voxels, f)
         cap = b * max_voxels
-        voxels = np.empty((cap, t, f), dtype=np.float32)
-        coors = np.empty((cap, 4), dtype=np.int32)
-        num = np.empty((cap,), dtype=np.int32)
-        fvo = np.empty((b + 1,), dtype=np.int32)
+        if out is not None:
+            voxels, coors, num, fvo = out[:4]
+            if (voxels.shape != (cap, t, f) or coors.shape != (cap, 4) or num.shape != (cap,)
+                    or fvo.shape != (b + 1,) or voxels.dtype != np.float32 or coors.dtype != np.int32
+                    or num.dtype != np.int32 or fvo.dtype != np.int32):
+                raise ValueError("out= buffers do not match this call's capacity shapes/dtypes")
+        else:
+            voxels = np.empty((cap, t, f), dtype=np.float32)
+            coors = np.empty((cap, 4), dtype=np.int32)
+            num = np.empty((cap,), dtype=np.int32)
+            fvo = np.empty((b + 1,), dtype=np.int32)
         _lib.check(lib.bvx_generate_batched_host(
             h, pts.ctypes.data, offs_p, b, f, max_voxels, voxels.ctypes.data, coors.ctypes.data,
             num.ctypes.data, fvo.ctypes.data, None), h)

@@ -177,6 +177,16 @@ int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m,
                     int32_t c, int32_t b, int32_t d, int32_t ny, int32_t nx,
                     float* canvas, void* stream);
 
+/* Optional per-kernel device timing: CUDA events are recorded on the call's
+ * stream around every kernel of the pipeline while enabled.  bvx_profile_read
+ * synchronises those events and returns accumulated milliseconds and launch
+ * counts per kernel slot: 0 k_insert, 1 k_verify (+ rank scan), 3 k_slot,
+ * 4 k_overflow, 5 k_gather (slots 2, 6, 7 unused). */
+#define BVX_PROFILE_SLOTS 8
+int bvx_profile_enable(bvx_handle* h, int32_t on);
+int bvx_profile_read(bvx_handle* h, double ms[BVX_PROFILE_SLOTS],
+                     int64_t launches[BVX_PROFILE_SLOTS], int32_t reset);
+
 /* Message of the last failing call on this handle (or, with h == NULL, of the
  * last failing handle-less call on this thread). */
 const char* bvx_last_error(const bvx_handle* h);
