@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -54,6 +55,9 @@ struct bvx_handle {
     std::vector<SegDesc> h_segs;
     std::vector<char> uploaded;  // byte image of the last uploaded layout
     bool all_plain = false;      // every frame of the current layout is one plain segment
+    long long table_used = 0;    // table entries the current layout touches
+    size_t l2_window_max = 0;    // cudaDevAttrMaxAccessPolicyWindowSize (0: persistence unavailable)
+    size_t l2_persist = 0;       // bytes of L2 set aside for persisting lines
     static const int kRing = 4;
     char* pin[kRing] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t pin_ev[kRing];
@@ -245,6 +249,22 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     };
     cudaError_t e = cudaSetDevice(h->device);
     if (e != cudaSuccess) return bail(e, "cudaSetDevice");
+    {   // L2 persistence for the hash tables: random atomics on L2-resident lines are ~5x
+        // faster than on lines that have to come back from HBM (tools/microbench.cu)
+        int maxp = 0, maxw = 0;
+        cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, h->device);
+        cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
+        // opt-in: measured no gain on B200
+        if (maxp > 0 && maxw > 0 && getenv("BVX_L2_PERSIST")) {
+            size_t cur = 0;
+            cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+            if (cur < (size_t)maxp) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)maxp);
+            cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+            h->l2_persist = cur;
+            h->l2_window_max = (size_t)maxw;
+        }
+        cudaGetLastError();
+    }
     const long long np = cfg->max_points, nf = cfg->max_frames;
     if (cfg->grid_kind == BVX_GRID_DENSE) h->table_slots = ncells * nf;
     else h->table_slots = 2 * np + 1024 * nf;
@@ -280,7 +300,14 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     }
     if ((e = cudaMemset(h->cnt, 0, (size_t)h->voxel_cap * 4)) != cudaSuccess) return bail(e, "memset cnt");
     if ((e = cudaMemset(h->counters, 0, 32)) != cudaSuccess) return bail(e, "memset counters");
-    if ((e = cudaMemset(h->d_state, 0, sizeof(FrameState) * (size_t)nf)) != cudaSuccess) return bail(e, "memset state");
+    {
+        FrameState z;
+        memset(&z, 0, sizeof z);
+        z.n_eff = 0x7FFFFFFF;
+        std::vector<FrameState> init((size_t)nf, z);
+        if ((e = cudaMemcpy(h->d_state, init.data(), sizeof(FrameState) * (size_t)nf, cudaMemcpyHostToDevice)) != cudaSuccess)
+            return bail(e, "init state");
+    }
     h->pin_bytes = sizeof(FrameDesc) * (size_t)nf + sizeof(SegDesc) * (size_t)h->seg_cap;
     for (int i = 0; i < bvx_handle::kRing; ++i) {
         if ((e = cudaMallocHost((void**)&h->pin[i], h->pin_bytes)) != cudaSuccess) return bail(e, "alloc pinned ring");
@@ -384,6 +411,7 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
     if (B > h->cfg.max_frames)
         return fail(h, BVX_ERR_WORKSPACE, "%d frames exceed the handle capacity max_frames=%d", B, h->cfg.max_frames);
     h->all_plain = all_plain;
+    h->table_used = tb;
     if (tb > h->table_slots || wd > h->words_cap || ck > h->chunks_cap || (int)h->h_segs.size() > h->seg_cap)
         return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, words %lld/%lld, segs %zu/%d)",
                     tb, h->table_slots, wd, h->words_cap, h->h_segs.size(), h->seg_cap);
@@ -421,6 +449,35 @@ struct Outputs {
     int mean_c;
     int coor_cols;
 };
+
+// Launch with the table region marked L2-persisting (per-launch access policy window).
+template <typename... KArgs, typename... Args>
+static void launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                     cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    int na = 0;
+    if (h->l2_window_max > 0 && h->table_used > 0) {
+        const size_t bytes = std::min((size_t)h->table_used * 8, h->l2_window_max);
+        attr[na].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[na].val.accessPolicyWindow.base_ptr = h->table;
+        attr[na].val.accessPolicyWindow.num_bytes = bytes;
+        attr[na].val.accessPolicyWindow.hitRatio =
+            bytes <= h->l2_persist ? 1.0f : (float)((double)h->l2_persist / (double)bytes);
+        attr[na].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[na].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    cudaLaunchKernelEx(&cfg, kern, args...);
+    g_launches += 1;
+}
 
 static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int f_in, int f_out,
                         int max_voxels, const Outputs& o, cudaStream_t st)
@@ -472,6 +529,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.coor_cols = o.coor_cols;
     p.ovf_cap = h->cfg.max_points;
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
+    p.dbg = getenv("BVX_DEBUG_MODE") ? atoi(getenv("BVX_DEBUG_MODE")) : 0;
     p.voxels = o.voxels;
     p.coors = o.coors;
     p.num_points = o.num_points;
@@ -480,20 +538,19 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
 
     const int T = p.T;
     const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
+    if (chunks > 65535 || B > 65535)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call and 67M points per frame");
     (void)max_words;
     if (chunks > 0) {
         ProfScope ps(h, 0, st);
-        k_insert<<<dim3(chunks, B), kBlock, 0, st>>>(p);
-        g_launches += 1;
+        launch_k(h, k_insert, dim3(B, chunks), kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
-        k_verify<<<dim3(std::max(chunks, 1), B), kBlock, 0, st>>>(p);
-        g_launches += 1;
+        launch_k(h, k_verify, dim3(std::max(chunks, 1), B), kBlock, 0, st, p);
     }
     if (chunks > 0) {
-        { ProfScope ps(h, 3, st); k_slot<<<dim3(chunks, B), kBlock, 0, st>>>(p); }
-        g_launches += 1;
+        { ProfScope ps(h, 3, st); launch_k(h, k_slot, dim3(std::min(chunks, 32), B), kBlock, 0, st, p); }
         if (T > kChainMaxT) {
             const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
             ProfScope ps(h, 4, st);
@@ -508,11 +565,10 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         const dim3 grid(tiles + chunks, B);
         ProfScope ps(h, 5, st);
         switch (T) {
-#define BVX_GS(TT) case TT: k_gather_small<TT><<<grid, kBlock, smem, st>>>(p, tiles); break;
+#define BVX_GS(TT) case TT: launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p, tiles); break;
             BVX_GS(1) BVX_GS(2) BVX_GS(3) BVX_GS(4) BVX_GS(5) BVX_GS(6) BVX_GS(7) BVX_GS(8)
 #undef BVX_GS
         }
-        g_launches += 1;
     } else {
         const int vt = std::max(1, kBlock / T);
         const int tiles = (cap + vt - 1) / vt;
@@ -522,8 +578,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         if (smem > 48 * 1024)
             CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ProfScope ps(h, 5, st);
-        k_gather<<<dim3(tiles + chunks, B), kBlock, smem, st>>>(p, tiles, vt);
-        g_launches += 1;
+        launch_k(h, k_gather, dim3(tiles + chunks, B), kBlock, smem, st, p, tiles, vt);
     }
     if (o.voxel_num) {
         CK(h, cudaMemcpyAsync(o.voxel_num, p.frame_voxel_offsets + B, 4, cudaMemcpyDeviceToDevice, st));

@@ -69,10 +69,14 @@ struct SegDesc {
 };
 
 struct FrameState {
-    int total;        // distinct in-range cells
+    int total;        // distinct in-range cells among the inserted points
     int m;            // voxels kept = min(total, cap)
     int istar;        // break cut-off: points with index >= istar are dropped
     int done_verify;  // chunks of k_verify finished (last-block detection); reset by the scanner
+    int next_chunk;   // k_insert: next chunk of the frame to hand out (in index order)
+    int distinct;     // k_insert: cells claimed so far by finished chunks
+    int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
+    int n_done;       // points that went through k_insert (prefix), published by the scan
 };
 
 struct Pipe {
@@ -100,6 +104,7 @@ struct Pipe {
     int coor_cols;       // 3 (single frame) or 4 (batched, batch index first)
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
+    int dbg;             // BVX_DEBUG_MODE experiments (0 = product behaviour)
     // outputs
     float* voxels;
     int* coors;
@@ -198,18 +203,49 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 }
 
 // ---------------------------------------------------------------- k_insert
-// grid (max chunks per frame, B).  Thread t of chunk c owns points
-// c*1024 + k*256 + t, k = 0..3: every warp-wide access is coalesced and a warp
-// covers exactly one 32-point mask word per k.
+// grid (B, max chunks per frame): x = frame, so blocks are dispatched chunk-row by
+// chunk-row across all frames.  A block takes the frame's next chunk in index order
+// from a ticket counter.  Thread t of chunk c owns points c*1024 + k*256 + t,
+// k = 0..3: every warp-wide access is coalesced and a warp covers exactly one
+// 32-point mask word per k.
+//
+// Break early exit (the reference's serial loop stops at the point that would open
+// voxel #cap): before taking its ticket a block reads the number of distinct cells
+// claimed by finished chunks.  If that already exceeds cap, every point that was
+// inserted lies in a chunk with a smaller ticket, so the cut-off index i* lies
+// before this chunk and the chunk is skipped (nothing it holds can be kept).
+// Skipping is monotone, so the inserted points always form a prefix [0, n_eff).
+//
+// Table protocol, CAS first, in ROUNDS (one atomic per point in flight, 4 per
+// thread -- the kernel is bound by L2 atomic round trips, tools/microbench2.cu):
+//   atomicCAS(empty -> {cell, i}):  was empty   -> new cell, I am a candidate
+//                                   same cell   -> atomicMin if my index is smaller
+//                                   other cell  -> probe the next slot
 __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
 {
-    const FrameDesc fr = p.frames[blockIdx.y];
-    const int base = blockIdx.x * kChunk;
-    if (base >= fr.n) return;
+    __shared__ int s_chunk;
+    __shared__ int s_new[kWarps];
+    const int f = blockIdx.x;
+    const FrameDesc fr = p.frames[f];
+    if ((int)blockIdx.y * kChunk >= fr.n) return;
+    FrameState* st = p.state + f;
+    if (threadIdx.x == 0) {
+        const int d = __ldcg(&st->distinct);           // read BEFORE the ticket (see above)
+        __threadfence();                               // ... and ordered before it
+        int c = atomicAdd(&st->next_chunk, 1);
+        if (!p.overflow_continue && d > p.cap && c * kChunk < fr.n) {
+            atomicMin(&st->n_eff, c * kChunk);
+            c = 0x7FFFFFF;                             // skipped
+        }
+        s_chunk = c;
+    }
+    __syncthreads();
+    const long long basel = (long long)s_chunk * kChunk;
+    if (basel >= fr.n) return;
+    const int base = (int)basel;
     unsigned long long* tbl = p.table + fr.tbl_off;
     int cell[kPts];
     unsigned int h[kPts];
-    unsigned long long e[kPts];
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
         const int i = base + k * kBlock + threadIdx.x;
@@ -220,46 +256,63 @@ __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
             cell[k] = cell_of(p.g, x, y, z);
         }
     }
+    unsigned int active = 0, needmin = 0, wonmask = 0, newmask = 0;
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
-        h[k] = 0; e[k] = 0;
+        h[k] = 0;
         if (cell[k] >= 0) {
             h[k] = fr.tbl_shift < 0 ? (unsigned)cell[k] : hash_cell((unsigned)cell[k], fr.tbl_shift);
-            e[k] = __ldcg(tbl + h[k]);
+            active |= 1u << k;
         }
     }
+    while (active) {
+        unsigned long long r[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const unsigned long long mine = ((unsigned long long)(unsigned)cell[k] << 32) |
+                                            (unsigned)(base + k * kBlock + threadIdx.x);
+            r[k] = 0;
+            if (active & (1u << k))
+                r[k] = (needmin & (1u << k)) ? atomicMin(tbl + h[k], mine)
+                                             : atomicCAS(tbl + h[k], kEmpty64, mine);
+        }
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const unsigned int bit = 1u << k;
+            if (!(active & bit)) continue;
+            const unsigned int i = (unsigned)(base + k * kBlock + threadIdx.x);
+            if (needmin & bit) {
+                if ((unsigned)r[k] > i) wonmask |= bit;
+                active &= ~bit;
+            } else if (r[k] == kEmpty64) {
+                wonmask |= bit; newmask |= bit; active &= ~bit;
+            } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
+                if ((unsigned)r[k] > i) needmin |= bit; else active &= ~bit;
+            } else {
+                h[k] = (h[k] + 1) & fr.tbl_mask;
+            }
+        }
+    }
+    int nnew = 0;
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
         const int i = base + k * kBlock + threadIdx.x;
-        bool won = false;
-        if (cell[k] >= 0) {
-            const unsigned int c = (unsigned)cell[k];
-            const unsigned long long mine = ((unsigned long long)c << 32) | (unsigned)i;
-            unsigned int hh = h[k];
-            unsigned long long ee = e[k];
-            while (true) {
-                if ((unsigned)(ee >> 32) == c) {              // my cell already has an entry
-                    if ((unsigned)ee > (unsigned)i) {
-                        const unsigned long long old = atomicMin(tbl + hh, mine);
-                        won = (unsigned)old > (unsigned)i;
-                    }
-                    break;
-                }
-                if (ee == kEmpty64) {                         // claim the empty slot
-                    const unsigned long long old = atomicCAS(tbl + hh, kEmpty64, mine);
-                    if (old == kEmpty64) { won = true; break; }
-                    ee = old;                                 // lost the race: re-examine this slot
-                    continue;
-                }
-                hh = (hh + 1) & fr.tbl_mask;                  // other cell: linear probe
-                ee = __ldcg(tbl + hh);
-            }
-            h[k] = hh;
-        }
         if (i < fr.n) p.slot[fr.pt_off + i] = cell[k] >= 0 ? (int)h[k] : -1;
-        const unsigned int b = __ballot_sync(0xffffffffu, won);
+        const unsigned int b = __ballot_sync(0xffffffffu, (wonmask >> k) & 1u);
+        nnew += __popc(__ballot_sync(0xffffffffu, (newmask >> k) & 1u));
         const int w = i >> 5;
         if ((threadIdx.x & 31) == 0 && w < fr.nwords) p.cand[fr.word_off + w] = b;
+    }
+    if (!p.overflow_continue) {
+        // publish the cells this chunk claimed; later tickets read it before they start
+        if ((threadIdx.x & 31) == 0) s_new[threadIdx.x >> 5] = nnew;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) t += s_new[w];
+            if (t) atomicAdd(&st->distinct, t);
+        }
     }
 }
 
@@ -298,18 +351,19 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem
 // Frame-level part, run by the last chunk of the frame to finish k_verify: scan the
 // chunk counts in place (chunkbase becomes the exclusive prefix), publish total / M /
 // i*, and -- for the last frame of the call -- the exclusive prefix of M over frames.
-__device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int* sm)
+__device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, int* sm)
 {
+    const int nchunks = (eff + kChunk - 1) / kChunk, nwords = (eff + 31) / 32;
     int* cb = p.chunkbase + fr.chunk_off;
     const int cap = p.cap;
     int carry = 0;
     int cut_chunk = -1, cut_base = 0;
-    for (int b0 = 0; b0 < fr.nchunks; b0 += kBlock) {
+    for (int b0 = 0; b0 < nchunks; b0 += kBlock) {
         const int c = b0 + threadIdx.x;
-        const int v = c < fr.nchunks ? __ldcg(cb + c) : 0;
+        const int v = c < nchunks ? __ldcg(cb + c) : 0;
         int tot;
         const int ex = carry + block_exclusive_scan(v, &tot, sm);
-        if (c < fr.nchunks) {
+        if (c < nchunks) {
             cb[c] = ex;
             if (ex <= cap && cap < ex + v) { cut_chunk = c; cut_base = ex; }  // at most one thread
         }
@@ -321,13 +375,14 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int* sm)
         p.state[f].total = total;
         p.state[f].m = min(total, cap);
         p.state[f].done_verify = 0;            // ready for the next call
-        if (!cut) p.state[f].istar = fr.n;
+        p.state[f].n_done = eff;
+        if (!cut) p.state[f].istar = eff;
     }
     if (cut && cut_chunk >= 0) {
         // the point that would open voxel #cap: (cap - prefix)-th first occurrence of this chunk
         int need = cap - cut_base;
         const int w0 = fr.word_off + cut_chunk * kChunkWords;
-        const int nw = min(kChunkWords, fr.nwords - cut_chunk * kChunkWords);
+        const int nw = min(kChunkWords, nwords - cut_chunk * kChunkWords);
         int w = 0;
         for (; w + 1 < nw; ++w)
             if (__ldcg(p.wordlocal + w0 + w + 1) > need) break;
@@ -368,17 +423,19 @@ __global__ void __launch_bounds__(kBlock) k_verify(const Pipe p)
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     const int base = blockIdx.x * kChunk;
-    if (base >= fr.n && !(fr.n == 0 && blockIdx.x == 0)) return;
+    const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));   // prefix that went through k_insert
+    if (base >= eff && !(eff == 0 && blockIdx.x == 0)) return;
+    const int nwords = (eff + 31) / 32;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const unsigned long long* tbl = p.table + fr.tbl_off;
-    if (fr.n > 0) {
+    if (eff > 0) {
         int sl[kPts];
         bool cd[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             const int i = base + k * kBlock + threadIdx.x;
             const int w = i >> 5;
-            const unsigned int cw = w < fr.nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
+            const unsigned int cw = w < nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
             cd[k] = (cw >> lane) & 1u;
             sl[k] = cd[k] ? __ldg(p.slot + fr.pt_off + i) : 0;
         }
@@ -398,7 +455,7 @@ __global__ void __launch_bounds__(kBlock) k_verify(const Pipe p)
             int tot;
             const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
             const int w = blockIdx.x * kChunkWords + lane;
-            if (w < fr.nwords) {
+            if (w < nwords) {
                 p.first[fr.word_off + w] = fw;
                 p.wordlocal[fr.word_off + w] = ex;
             }
@@ -409,66 +466,89 @@ __global__ void __launch_bounds__(kBlock) k_verify(const Pipe p)
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0)
-        s_last = (atomicAdd(&p.state[f].done_verify, 1) == max(fr.nchunks, 1) - 1);
+        s_last = (atomicAdd(&p.state[f].done_verify, 1) == max((eff + kChunk - 1) / kChunk, 1) - 1);
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    frame_scan(p, fr, f, sm);
+    frame_scan(p, fr, f, eff, sm);
 }
 
 // ---------------------------------------------------------------- k_slot
-// grid (max chunks per frame, B).  Chunks at or beyond the break cut-off exit at once.
+// grid (gx, B): block x of frame f walks chunks x, x+gx, ... below the break
+// cut-off, so the launch carries no blocks that only exit.  Same round structure as
+// k_insert: per round one atomic per point in flight.
 __global__ void __launch_bounds__(kBlock) k_slot(const Pipe p)
 {
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
-    const int base = blockIdx.x * kChunk;
-    if (base >= fr.n) return;
-    const int istar = p.state[f].istar;
-    if (base >= istar) return;
+    const int lim = min(p.state[f].n_done, p.state[f].istar);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // k_insert's per-frame counters, for the next call
+        p.state[f].next_chunk = 0;
+        p.state[f].distinct = 0;
+        p.state[f].n_eff = 0x7FFFFFFF;
+    }
     const unsigned long long* tbl = p.table + fr.tbl_off;
-    int sl[kPts];
+    const int T = p.T;
+    for (int base = blockIdx.x * kChunk; base < lim; base += gridDim.x * kChunk) {
+        int sl[kPts];
 #pragma unroll
-    for (int k = 0; k < kPts; ++k) {
-        const int i = base + k * kBlock + threadIdx.x;
-        sl[k] = (i < fr.n && i < istar) ? __ldg(p.slot + fr.pt_off + i) : -1;
-    }
-    unsigned long long e[kPts];
-#pragma unroll
-    for (int k = 0; k < kPts; ++k) e[k] = sl[k] >= 0 ? __ldcg(tbl + sl[k]) : 0ull;
-    int rank[kPts];
-#pragma unroll
-    for (int k = 0; k < kPts; ++k) {
-        rank[k] = 0x7FFFFFFF;
-        if (sl[k] >= 0) {
-            const unsigned int fidx = (unsigned)e[k];
-            const int w = fidx >> 5;
-            rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
-                      __ldg(p.wordlocal + fr.word_off + w) +
-                      __popc(__ldg(p.first + fr.word_off + w) & ((1u << (fidx & 31)) - 1u));
+        for (int k = 0; k < kPts; ++k) {
+            const int i = base + k * kBlock + threadIdx.x;
+            sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;
         }
-    }
+        unsigned long long e[kPts];
 #pragma unroll
-    for (int k = 0; k < kPts; ++k) {
-        if (rank[k] >= p.cap) continue;   // out of range, cut off, or (continue mode) beyond the cap
-        const int i = base + k * kBlock + threadIdx.x;
-        const size_t g = (size_t)f * p.cap + rank[k];
-        int* b = p.bucket + g * p.T;
-        if (p.T <= kChainMaxT) {
+        for (int k = 0; k < kPts; ++k) e[k] = sl[k] >= 0 ? __ldcg(tbl + sl[k]) : 0ull;
+        int rank[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            rank[k] = 0x7FFFFFFF;
+            if (sl[k] >= 0) {
+                const unsigned int fidx = (unsigned)e[k];
+                const int w = fidx >> 5;
+                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
+                          __ldg(p.wordlocal + fr.word_off + w) +
+                          __popc(__ldg(p.first + fr.word_off + w) & ((1u << (fidx & 31)) - 1u));
+            }
+        }
+        // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
+        if (T <= kChainMaxT) {
             // sorted insertion: slot j ends up holding the (j+1)-th smallest index offered
-            int cur = i;
-            for (int j = 0; j < p.T; ++j) {
-                const int old = atomicMin(b + j, cur);
-                if (old == kEmptyIdx) break;
-                cur = max(old, cur);
+            int cur[kPts];
+            int* b[kPts];
+            unsigned int active = 0;
+#pragma unroll
+            for (int k = 0; k < kPts; ++k) {
+                cur[k] = base + k * kBlock + threadIdx.x;
+                b[k] = p.bucket + ((size_t)f * p.cap + (rank[k] < p.cap ? rank[k] : 0)) * T;
+                if (rank[k] < p.cap) active |= 1u << k;
+            }
+            for (int j = 0; j < T && active; ++j) {
+                int old[kPts];
+#pragma unroll
+                for (int k = 0; k < kPts; ++k)
+                    old[k] = (active & (1u << k)) ? atomicMin(b[k] + j, cur[k]) : 0;
+#pragma unroll
+                for (int k = 0; k < kPts; ++k) {
+                    if (active & (1u << k)) {
+                        if (old[k] == kEmptyIdx) active &= ~(1u << k);
+                        else cur[k] = max(old[k], cur[k]);
+                    }
+                }
             }
         } else {
-            const int c = atomicAdd(p.cnt + g, 1);
-            if (c < p.T) {
-                b[c] = i;
-            } else {
-                const int o = atomicAdd(&p.counters[1], 1);
-                if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
+#pragma unroll
+            for (int k = 0; k < kPts; ++k) {
+                if (rank[k] >= p.cap) continue;
+                const int i = base + k * kBlock + threadIdx.x;
+                const size_t g = (size_t)f * p.cap + rank[k];
+                const int c = atomicAdd(p.cnt + g, 1);
+                if (c < T) {
+                    p.bucket[g * T + c] = i;
+                } else {
+                    const int o = atomicAdd(&p.counters[1], 1);
+                    if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
+                }
             }
         }
     }
@@ -501,14 +581,16 @@ __global__ void __launch_bounds__(kBlock) k_overflow(const Pipe p)
 __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, int chunk)
 {
     const int base = chunk * kChunk;
-    if (base >= fr.n) return;
+    const int eff = p.state[blockIdx.y].n_done;
+    if (base >= eff) return;
+    const int nwords = (eff + 31) / 32;
     const int lane = threadIdx.x & 31;
     unsigned long long* tbl = p.table + fr.tbl_off;
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
         const int i = base + k * kBlock + threadIdx.x;
         const int w = i >> 5;
-        const unsigned int cw = w < fr.nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
+        const unsigned int cw = w < nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
         if ((cw >> lane) & 1u) tbl[__ldg(p.slot + fr.pt_off + i)] = kEmpty64;
     }
 }
