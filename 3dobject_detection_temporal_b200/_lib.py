@@ -17,7 +17,7 @@ BVX_ERR_WORKSPACE = 3
 BVX_ERR_NO_DEVICE = 4
 
 PROFILE_SLOTS = 8
-KERNEL_NAMES = ["k_chain", "", "", "", "", "k_gather", "", ""]
+KERNEL_NAMES = ["k_insert", "k_verify", "", "k_slot", "k_overflow", "k_gather", "", ""]
 OVERFLOW = {"break": 0, "continue": 1}
 GRID = {"hashed": 0, "dense": 1}
 
@@ -74,8 +74,6 @@ SYMBOLS = {
     "bvx_profile_enable": (ctypes.c_int, [_vp, _i32]),
     "bvx_profile_read": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64),
                                         _i32]),
-    "bvx_chain_trace": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_int64), _i32, ctypes.POINTER(_i32),
-                                       ctypes.POINTER(_i32)]),
     "bvx_last_error": (ctypes.c_char_p, [_vp]),
     "bvx_launch_count": (ctypes.c_int64, []),
     "bvx_abi_version": (ctypes.c_int, []),

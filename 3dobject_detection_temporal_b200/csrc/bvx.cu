@@ -30,23 +30,25 @@ struct bvx_handle {
     int device;
     // capacities
     long long table_slots;
+    long long words_cap;
     long long voxel_cap;   // max_frames * max_voxels
     // device workspace
-    Entry* table = nullptr;
-    unsigned int* vslot = nullptr;
+    unsigned long long* table = nullptr;
+    int* slot = nullptr;
+    unsigned int* cand = nullptr;
+    unsigned int* first = nullptr;
+    int* wordlocal = nullptr;
+    int* chunkbase = nullptr;
+    long long chunks_cap = 0;
     int* bucket = nullptr;
-    unsigned int* dead = nullptr;
+    int* cnt = nullptr;
+    int2* ovf = nullptr;
     int* counters = nullptr;
-    long long* trace = nullptr;   // diagnostics (bvx_chain_trace)
-    long long trace_tickets = 0;
-    long long last_tickets = 0;
     FrameDesc* d_frames = nullptr;
     SegDesc* d_segs = nullptr;
     FrameState* d_state = nullptr;
     int* d_offsets_scratch = nullptr;  // frame_voxel_offsets when the caller passes none
     size_t ws_bytes = 0;
-    long long slots_per_frame = 0;
-    int chain_blocks = 0;
     int seg_cap = 0;
     // descriptor upload
     std::vector<FrameDesc> h_frames;
@@ -184,8 +186,9 @@ extern "C" int bvx_destroy(bvx_handle* h)
 {
     if (!h) return BVX_OK;
     cudaSetDevice(h->device);
-    cudaFree(h->table); cudaFree(h->vslot); cudaFree(h->bucket); cudaFree(h->dead);
-    cudaFree(h->counters); cudaFree(h->trace); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
+    cudaFree(h->table); cudaFree(h->slot); cudaFree(h->cand); cudaFree(h->first);
+    cudaFree(h->wordlocal); cudaFree(h->chunkbase); cudaFree(h->bucket); cudaFree(h->cnt); cudaFree(h->ovf);
+    cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
     cudaFree(h->d_offsets_scratch);
     cudaFree(h->dev_points); cudaFree(h->dev_voxels); cudaFree(h->dev_coors);
     cudaFree(h->dev_num); cudaFree(h->dev_offs);
@@ -262,43 +265,48 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
         }
         cudaGetLastError();
     }
-    const long long nf = cfg->max_frames;
-    // The chain numbers voxels exactly, so a frame's table never holds more than
-    // max_voxels live cells plus the cells one chunk may claim beyond the cap.
-    h->slots_per_frame = cfg->grid_kind == BVX_GRID_DENSE
-                             ? ncells
-                             : (1ll << std::max(10, ilog2_ceil(2ull * ((unsigned long long)cfg->max_voxels + kCChunk))));
-    h->table_slots = h->slots_per_frame * nf;
+    const long long np = cfg->max_points, nf = cfg->max_frames;
+    if (cfg->grid_kind == BVX_GRID_DENSE) h->table_slots = ncells * nf;
+    else h->table_slots = 2 * np + 1024 * nf;
+    h->words_cap = np / 32 + 2 * nf + 8;
     h->voxel_cap = (long long)cfg->max_voxels * nf;
     h->seg_cap = (int)std::max<long long>(nf, 64);
     if ((e = dalloc(h, &h->table, (size_t)h->table_slots)) != cudaSuccess) return bail(e, "alloc table");
-    if ((e = dalloc(h, &h->vslot, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc vslot");
+    if ((e = dalloc(h, &h->slot, (size_t)np)) != cudaSuccess) return bail(e, "alloc slot");
+    if ((e = dalloc(h, &h->cand, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc cand");
+    if ((e = dalloc(h, &h->first, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc first");
+    if ((e = dalloc(h, &h->wordlocal, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc wordlocal");
+    h->chunks_cap = np / kChunk + 2 * nf + 8;
+    if ((e = dalloc(h, &h->chunkbase, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkbase");
     if ((e = dalloc(h, &h->bucket, (size_t)h->voxel_cap * cfg->max_num_points)) != cudaSuccess) return bail(e, "alloc bucket");
-    if ((e = dalloc(h, &h->dead, (size_t)nf * kCChunk)) != cudaSuccess) return bail(e, "alloc dead list");
+    if ((e = dalloc(h, &h->cnt, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc cnt");
+    if (cfg->max_num_points > kChainMaxT)
+        if ((e = dalloc(h, &h->ovf, (size_t)np)) != cudaSuccess) return bail(e, "alloc ovf");
     if ((e = dalloc(h, &h->counters, 8)) != cudaSuccess) return bail(e, "alloc counters");
     if ((e = dalloc(h, &h->d_frames, (size_t)nf)) != cudaSuccess) return bail(e, "alloc frames");
     if ((e = dalloc(h, &h->d_segs, (size_t)h->seg_cap)) != cudaSuccess) return bail(e, "alloc segs");
     if ((e = dalloc(h, &h->d_state, (size_t)nf)) != cudaSuccess) return bail(e, "alloc state");
     if ((e = dalloc(h, &h->d_offsets_scratch, (size_t)nf + 1)) != cudaSuccess) return bail(e, "alloc offsets");
     // one-time initialisation; every call leaves the workspace clean again
-    if ((e = cudaMemset(h->table, 0xFF, (size_t)h->table_slots * sizeof(Entry))) != cudaSuccess) return bail(e, "memset table");
+    if ((e = cudaMemset(h->table, 0xFF, (size_t)h->table_slots * 8)) != cudaSuccess) return bail(e, "memset table");
+    {
+        const size_t nb = (size_t)h->voxel_cap * cfg->max_num_points;
+        std::vector<int> fillv(std::min<size_t>(nb, 1 << 20), kEmptyIdx);
+        for (size_t off = 0; off < nb; off += fillv.size()) {
+            const size_t c = std::min(fillv.size(), nb - off);
+            if ((e = cudaMemcpy(h->bucket + off, fillv.data(), c * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+                return bail(e, "init bucket");
+        }
+    }
+    if ((e = cudaMemset(h->cnt, 0, (size_t)h->voxel_cap * 4)) != cudaSuccess) return bail(e, "memset cnt");
     if ((e = cudaMemset(h->counters, 0, 32)) != cudaSuccess) return bail(e, "memset counters");
     {
         FrameState z;
         memset(&z, 0, sizeof z);
-        z.istar = 0x7FFFFFFF;
+        z.n_eff = 0x7FFFFFFF;
         std::vector<FrameState> init((size_t)nf, z);
         if ((e = cudaMemcpy(h->d_state, init.data(), sizeof(FrameState) * (size_t)nf, cudaMemcpyHostToDevice)) != cudaSuccess)
             return bail(e, "init state");
-    }
-    if ((e = cudaFuncSetAttribute(k_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ChainSmem))) != cudaSuccess)
-        return bail(e, "k_chain shared memory");
-    {
-        int dev_sms = 0, per_sm = 0;
-        cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->device);
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, kCT, sizeof(ChainSmem))) != cudaSuccess)
-            return bail(e, "k_chain occupancy");
-        h->chain_blocks = std::max(1, dev_sms * std::max(1, per_sm));
     }
     h->pin_bytes = sizeof(FrameDesc) * (size_t)nf + sizeof(SegDesc) * (size_t)h->seg_cap;
     for (int i = 0; i < bvx_handle::kRing; ++i) {
@@ -326,21 +334,18 @@ struct FrameSpec {
     int with_dt;
 };
 
-static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, int cap, cudaStream_t st,
-                         int* max_n_out, bool* all_aligned)
+static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
+                         int* max_n_out, int* max_words_out, bool* all_aligned)
 {
     const int B = (int)frames.size();
     h->h_frames.assign(B, FrameDesc());
     h->h_segs.clear();
-    long long pt = 0, tb = 0;
-    int max_n = 0;
+    long long pt = 0, wd = 0, tb = 0, ck = 0;
+    int max_n = 0, max_words = 0;
     bool all_plain = true;
     *all_aligned = true;
-    // hashed: slots for (cap live cells + one chunk of cells claimed beyond the cap) at load <= 1/2
-    const int lg = std::max(10, ilog2_ceil(2ull * ((unsigned long long)cap + kCChunk)));
     for (int f = 0; f < B; ++f) {
         FrameDesc& fd = h->h_frames[f];
-        memset(&fd, 0, sizeof fd);
         fd.seg_begin = (int)h->h_segs.size();
         fd.seg_count = frames[f].k;
         long long n = 0;
@@ -368,25 +373,38 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, in
             h->h_segs.push_back(sd);
             fd.seg_count = 1;
         }
-        if (n > 0x7FFFFFF0ll - kCChunk) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
+        if (n > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
         fd.n = (int)n;
         fd.pts0 = nullptr;
         if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform)
             fd.pts0 = frames[f].sweeps[0].points;
         else if (n > 0)
             all_plain = false;
+        fd.chunk_off = (int)ck;
+        fd.nchunks = (int)((n + kChunk - 1) / kChunk);
+        ck += fd.nchunks;
+        fd.pt_off = (int)pt;
+        fd.word_off = (int)wd;
+        fd.nwords = (int)((n + 31) / 32);
         fd.tbl_off = (unsigned long long)tb;
         if (h->cfg.grid_kind == BVX_GRID_DENSE) {
             fd.tbl_shift = -1;
             fd.tbl_mask = 0xFFFFFFFFu;
             tb += h->ncells;
         } else {
+            int lg = std::max(10, ilog2_ceil((unsigned long long)n + 1));
+            if ((1ll << lg) > h->ncells && h->ncells >= 1024) {
+                // table never needs more slots than there are cells
+                lg = std::max(10, ilog2_ceil((unsigned long long)h->ncells + 1));
+            }
             fd.tbl_shift = 32 - lg;
             fd.tbl_mask = (1u << lg) - 1u;
             tb += (1ll << lg);
         }
         pt += n;
+        wd += fd.nwords;
         max_n = std::max(max_n, fd.n);
+        max_words = std::max(max_words, fd.nwords);
     }
     if (pt > h->cfg.max_points)
         return fail(h, BVX_ERR_WORKSPACE, "%lld points exceed the handle capacity max_points=%d", pt, h->cfg.max_points);
@@ -394,10 +412,11 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, in
         return fail(h, BVX_ERR_WORKSPACE, "%d frames exceed the handle capacity max_frames=%d", B, h->cfg.max_frames);
     h->all_plain = all_plain;
     h->table_used = tb;
-    if (tb > h->table_slots || (int)h->h_segs.size() > h->seg_cap)
-        return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, segs %zu/%d)",
-                    tb, h->table_slots, h->h_segs.size(), h->seg_cap);
+    if (tb > h->table_slots || wd > h->words_cap || ck > h->chunks_cap || (int)h->h_segs.size() > h->seg_cap)
+        return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, words %lld/%lld, segs %zu/%d)",
+                    tb, h->table_slots, wd, h->words_cap, h->h_segs.size(), h->seg_cap);
     *max_n_out = max_n;
+    *max_words_out = max_words;
 
     const size_t fb = sizeof(FrameDesc) * (size_t)B, sb = sizeof(SegDesc) * h->h_segs.size();
     std::vector<char> img(fb + sb);
@@ -479,9 +498,9 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     if (o.mean && (o.mean_c < 1 || o.mean_c > f_out))
         return fail(h, BVX_ERR_BAD_ARGUMENT, "mean_channels=%d must be in [1, %d]", o.mean_c, f_out);
     CK(h, cudaSetDevice(h->device));
-    int max_n = 0;
+    int max_n = 0, max_words = 0;
     bool aligned = true;
-    int rc = upload_layout(h, frames, cap, st, &max_n, &aligned);
+    int rc = upload_layout(h, frames, st, &max_n, &max_words, &aligned);
     if (rc) return rc;
 
     Pipe p;
@@ -491,22 +510,26 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.segs = h->d_segs;
     p.state = h->d_state;
     p.table = h->table;
-    p.vslot = h->vslot;
+    p.slot = h->slot;
+    p.cand = h->cand;
+    p.first = h->first;
+    p.wordlocal = h->wordlocal;
+    p.chunkbase = h->chunkbase;
     p.bucket = h->bucket;
-    p.dead = h->dead;
-    p.nframes = B;
-    p.rows = std::max(1, (max_n + kCChunk - 1) / kCChunk);
+    p.cnt = h->cnt;
+    p.ovf = h->ovf;
     p.counters = h->counters;
-    p.trace = ((long long)p.rows * B <= h->trace_tickets) ? h->trace : nullptr;
-    h->last_tickets = 0;
     p.frame_voxel_offsets = o.frame_voxel_offsets ? o.frame_voxel_offsets : h->d_offsets_scratch;
+    p.nframes = B;
     p.f_in = f_in;
     p.f_out = f_out;
     p.T = h->cfg.max_num_points;
     p.cap = cap;
     p.overflow_continue = h->cfg.overflow_mode == BVX_OVERFLOW_CONTINUE;
     p.coor_cols = o.coor_cols;
+    p.ovf_cap = h->cfg.max_points;
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
+    p.dbg = getenv("BVX_DEBUG_MODE") ? atoi(getenv("BVX_DEBUG_MODE")) : 0;
     p.voxels = o.voxels;
     p.coors = o.coors;
     p.num_points = o.num_points;
@@ -514,39 +537,48 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.mean_c = o.mean_c;
 
     const int T = p.T;
-    if (B > 65535) return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call");
-    if ((long long)p.rows * B > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "too many chunks");
-    {   // chain: persistent blocks, never more than there are tickets
-        const long long tickets = (long long)p.rows * B;
-        const int blocks = (int)std::min<long long>(tickets, h->chain_blocks);
-        h->last_tickets = tickets;
-        if (p.trace) CK(h, cudaMemsetAsync(h->trace, 0, (size_t)tickets * 64, st));
+    const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
+    if (chunks > 65535 || B > 65535)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call and 67M points per frame");
+    (void)max_words;
+    if (chunks > 0) {
         ProfScope ps(h, 0, st);
-        launch_k(h, k_chain, dim3(blocks), kCT, sizeof(ChainSmem), st, p);
+        launch_k(h, k_insert, dim3(B, chunks), kBlock, 0, st, p);
     }
-    const bool small = T <= 8 && f_out == 4 && p.vec4 && h->all_plain;
+    {   // always runs: an empty frame still needs its state and the offsets written
+        ProfScope ps(h, 1, st);
+        launch_k(h, k_verify, dim3(std::max(chunks, 1), B), kBlock, 0, st, p);
+    }
+    if (chunks > 0) {
+        { ProfScope ps(h, 3, st); launch_k(h, k_slot, dim3(std::min(chunks, 32), B), kBlock, 0, st, p); }
+        if (T > kChainMaxT) {
+            const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
+            ProfScope ps(h, 4, st);
+            k_overflow<<<ob, kBlock, 0, st>>>(p);
+            g_launches += 1;
+        }
+    }
+    const bool small = T <= kChainMaxT && f_out == 4 && p.vec4 && h->all_plain;
     if (small) {
         const int tiles = (cap + kBlock - 1) / kBlock;
         const size_t smem = (size_t)kWarps * 32 * T * 16;
-        const dim3 grid(tiles, B);
+        const dim3 grid(tiles + chunks, B);
         ProfScope ps(h, 5, st);
         switch (T) {
-#define BVX_GS(TT) case TT: launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p); break;
+#define BVX_GS(TT) case TT: launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p, tiles); break;
             BVX_GS(1) BVX_GS(2) BVX_GS(3) BVX_GS(4) BVX_GS(5) BVX_GS(6) BVX_GS(7) BVX_GS(8)
 #undef BVX_GS
         }
     } else {
-        // tile: as many voxels as keep the staged rows under ~32 KB (at least one)
-        const int vt = std::max(1, std::min(kBlock, (32 * 1024) / (T * f_out * 4)));
+        const int vt = std::max(1, kBlock / T);
         const int tiles = (cap + vt - 1) / vt;
-        const size_t smem = (size_t)((vt + 3) & ~3) * 4 + (size_t)vt * T * f_out * 4;
+        const size_t smem = (size_t)((vt * T + 3) & ~3) * 4 + (size_t)vt * T * f_out * 4;
         if (smem > 200 * 1024)
             return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", smem);
         if (smem > 48 * 1024)
             CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        if (tiles > 0x7FFFFFFF / 2) return fail(h, BVX_ERR_BAD_ARGUMENT, "too many gather tiles");
         ProfScope ps(h, 5, st);
-        launch_k(h, k_gather, dim3(tiles, B), kBlock, smem, st, p, vt);
+        launch_k(h, k_gather, dim3(tiles + chunks, B), kBlock, smem, st, p, tiles, vt);
     }
     if (o.voxel_num) {
         CK(h, cudaMemcpyAsync(o.voxel_num, p.frame_voxel_offsets + B, 4, cudaMemcpyDeviceToDevice, st));
@@ -741,28 +773,6 @@ extern "C" int bvx_generate_host(bvx_handle* h, const float* points, int32_t n, 
 }
 
 // ------------------------------------------------------------------ profiling
-extern "C" int bvx_chain_trace(bvx_handle* h, int64_t* out, int32_t max_tickets, int32_t* tickets, int32_t* chunk_points)
-{
-    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
-    CK(h, cudaSetDevice(h->device));
-    if (chunk_points) *chunk_points = kCChunk;
-    if (!out) {   // arm: allocate room for max_tickets tickets; later calls record into it
-        cudaFree(h->trace);
-        h->trace = nullptr;
-        h->trace_tickets = 0;
-        if (max_tickets > 0) {
-            CK(h, cudaMalloc((void**)&h->trace, (size_t)max_tickets * 64));
-            h->trace_tickets = max_tickets;
-        }
-        return BVX_OK;
-    }
-    CK(h, cudaDeviceSynchronize());
-    const long long n = std::min<long long>(h->last_tickets, std::min<long long>(max_tickets, h->trace_tickets));
-    if (tickets) *tickets = (int32_t)n;
-    if (n > 0) CK(h, cudaMemcpy(out, h->trace, (size_t)n * 64, cudaMemcpyDeviceToHost));
-    return BVX_OK;
-}
-
 extern "C" int bvx_profile_enable(bvx_handle* h, int32_t on)
 {
     if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");

@@ -1,30 +1,25 @@
 // bvx_kernels.cuh -- sm_100a kernels of the voxelization hot path.
 //
-// One pass of VoxelGenerator.generate over B frames is TWO kernels (DESIGN.md has
-// the data layout and the per-kernel roofline):
-//
-//   k_chain   persistent blocks take (chunk, frame) tickets; a chunk is kCChunk
-//             consecutive points of one frame.  Everything that does not depend on
-//             earlier points -- load, cell key, de-duplication of the chunk's
-//             cells and the input-order rank of every point among the chunk's
-//             points of the same cell -- is done in shared memory first.  Then the
-//             block waits for the frame's previous chunk (a release/acquire
-//             counter: the frame's chunks form a CHAIN, which is what makes the
-//             reference's serial first-come numbering exact in one pass), resolves
-//             one representative per distinct cell against the frame's table in
-//             L2 (atomicCAS: empty -> new voxel, else the voxel id comes back),
-//             numbers the new voxels by a block scan in input order starting at
-//             the frame's running voxel count, finds the break cut-off i* / the
-//             cap exactly, reserves the points' slots with one atomicAdd per cell
-//             and hands the chain to the next chunk.  Off the chain it writes
-//             each kept point's index into its (voxel, slot) bucket entry.
-//   k_gather  per voxel: rows -> voxels (zero padded), coordinates, num_points,
-//             optional fused mean VFE; also returns the workspace to its clean
-//             state (table entries of the frame's voxels, counts, chain state),
-//             so no call ever needs a memset.
-//
+// Pipeline (one pass of VoxelGenerator.generate over B frames; DESIGN.md has the
+// data layout and the per-kernel roofline).  Work is cut into chunks of 1024
+// consecutive points (256 threads x 4 points, all four loads in flight at once):
+//   k_insert  per chunk : cell key -> table slot; first occurrence by 64-bit
+//                         atomicCAS/atomicMin on {cell:32 | point index:32};
+//                         candidate bit per point ("held the minimum when I left")
+//   k_verify  per chunk : candidate -> true first-occurrence bits, per-word and
+//                         per-chunk counts; the LAST chunk of a frame scans the
+//                         chunk counts (first-come voxel ranks, M = min(total,
+//                         cap), break cut-off i*), the last frame prefix-sums M
+//   k_slot    per chunk : voxel id = rank of the voxel's first point; slot inside
+//                         the voxel in input order (sorted atomicMin chain for
+//                         T <= 8, count + bucket for larger T)
+//   k_overflow          : (T > 8) T-smallest selection for crowded voxels
+//   k_gather  per voxel : rows -> voxels (zero padded), coordinates from the first
+//                         point, num_points, optional fused mean VFE; extra blocks
+//                         of the same launch reset the table entries the frame
+//                         touched, so the next call needs no memset
 // Everything is fp32 / int32; nothing here is a contraction, hence no tensor
-// cores: the bounds are HBM bandwidth and L2 atomic round trips on the chain.
+// cores: the bounds are HBM bandwidth and L2 random-access / atomic throughput.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -32,36 +27,13 @@
 namespace bvx {
 
 constexpr unsigned long long kEmpty64 = 0xFFFFFFFFFFFFFFFFull;
-constexpr unsigned int kEmpty32 = 0xFFFFFFFFu;
-constexpr int kVidUnset = -1;                    // entry claimed, voxel number not written yet
-constexpr int kVidDead = -2;                     // cell first seen when the frame was already full
-constexpr int kBlock = 256;                      // gather / VFE / scatter block
+constexpr int kEmptyIdx = 0x7FFFFFFF;
+constexpr int kChainMaxT = 8;        // T <= 8: sorted atomicMin chain; else count+bucket
+constexpr int kBlock = 256;
+constexpr int kPts = 4;              // points per thread
+constexpr int kChunk = kBlock * kPts;  // 1024 points per chunk
+constexpr int kChunkWords = kChunk / 32;
 constexpr int kWarps = kBlock / 32;
-
-// chain kernel geometry
-#ifndef BVX_CHAIN_THREADS
-#define BVX_CHAIN_THREADS 1024
-#endif
-#ifndef BVX_CHAIN_PTS
-#define BVX_CHAIN_PTS 4
-#endif
-constexpr int kCT = BVX_CHAIN_THREADS;           // threads per chain block
-constexpr int kCP = BVX_CHAIN_PTS;               // points per thread
-constexpr int kCChunk = kCT * kCP;               // points per chunk
-constexpr int kCWarps = kCT / 32;
-constexpr int kLSlots = 2 * kCChunk;             // shared-memory hash slots per chunk
-constexpr int kLShift = 32 - (kCChunk == 4096 ? 13 : kCChunk == 2048 ? 12 : kCChunk == 8192 ? 14 : 11);
-static_assert((1 << (32 - kLShift)) == kLSlots, "kCChunk must be 1024, 2048, 4096 or 8192");
-static_assert(kCChunk <= 65535, "local indices are stored as uint16");
-constexpr unsigned int kLEnd = 0xFFFFu;
-
-// Table entry.  key = {cell:32 (high) | points offered to the cell so far:32 (low)};
-// all ones = empty.  One 64-bit atomic on key both claims a cell and reserves slots.
-struct __align__(16) Entry {
-    unsigned long long key;
-    int vid;        // voxel number of the cell in first-come order (kVidUnset / kVidDead)
-    int pad_;
-};
 
 struct GridParams {
     float lo[3];
@@ -76,9 +48,13 @@ struct FrameDesc {
     unsigned int tbl_mask;       // slots - 1 (hashed)
     int tbl_shift;               // 32 - log2(slots) (hashed); -1 => dense (slot = cell)
     int n;                       // points in the frame (all segments)
+    int pt_off;                  // base into slot[]
+    int word_off;                // base into cand/first/wordlocal
+    int nwords;
+    int chunk_off;               // base into chunkbase[]
+    int nchunks;
     int seg_begin;
     int seg_count;
-    int pad_;
 };
 
 struct SegDesc {
@@ -92,38 +68,43 @@ struct SegDesc {
     float dt;
 };
 
-// Per-frame chain state.  `done` is the release/acquire word of the chain.
 struct FrameState {
-    int done;      // chunks of the frame that have been published; bit 30 = closed (cut-off found)
-    int nvox;      // voxels created so far (<= cap)
-    int istar;     // break cut-off: points with index >= istar are dropped
-    int ndead;     // entries of the dead list (cells claimed beyond the cap)
-    int m;         // result: voxels of the frame (read by k_gather; not reset)
-    int pad_[3];
+    int total;        // distinct in-range cells among the inserted points
+    int m;            // voxels kept = min(total, cap)
+    int istar;        // break cut-off: points with index >= istar are dropped
+    int done_verify;  // chunks of k_verify finished (last-block detection); reset by the scanner
+    int next_chunk;   // k_insert: next chunk of the frame to hand out (in index order)
+    int distinct;     // k_insert: cells claimed so far by finished chunks
+    int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
+    int n_done;       // points that went through k_insert (prefix), published by the scan
 };
-constexpr int kClosedBit = 1 << 30;
 
 struct Pipe {
     GridParams g;
     const FrameDesc* frames;
     const SegDesc* segs;
     FrameState* state;
-    Entry* table;
-    unsigned int* vslot;         // [B, cap] table slot of the voxel (for the reset)
-    int* bucket;                 // [B, cap, T] point index per (voxel, slot)
-    unsigned int* dead;          // [B, kCChunk] table slots of dead cells
-    int* counters;               // [0] ticket, [1] frames done
+    unsigned long long* table;
+    int* slot;
+    unsigned int* cand;
+    unsigned int* first;
+    int* wordlocal;      // exclusive prefix of first-occurrence counts inside the word's chunk
+    int* chunkbase;      // per chunk: count, then exclusive prefix over the frame's chunks
+    int* bucket;
+    int* cnt;
+    int2* ovf;
+    int* counters;       // [0] frames-done ticket, [1] overflow count
     int* frame_voxel_offsets;
-    long long* trace;            // optional [tickets, 8] globaltimer stamps of thread 0 (diagnostics)
     int nframes;
-    int rows;                    // chunk rows = max(1, ceil(max n / kCChunk))
     int f_in;
     int f_out;
     int T;
-    int cap;                     // per-frame max_voxels of this call
+    int cap;             // per-frame max_voxels of this call
     int overflow_continue;
-    int coor_cols;               // 3 (single frame) or 4 (batched, batch index first)
-    int vec4;                    // f_in == 4 and every segment pointer 16-byte aligned
+    int coor_cols;       // 3 (single frame) or 4 (batched, batch index first)
+    int ovf_cap;
+    int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
+    int dbg;             // BVX_DEBUG_MODE experiments (0 = product behaviour)
     // outputs
     float* voxels;
     int* coors;
@@ -131,24 +112,6 @@ struct Pipe {
     float* mean_out;
     int mean_c;
 };
-
-__device__ __forceinline__ int ld_acquire(const int* p)
-{
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ long long gtime()
-{
-    long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-#define BVX_TRACE(slot) do { if (p.trace && tid == 0) p.trace[(size_t)g * 8 + (slot)] = gtime(); } while (0)
-__device__ __forceinline__ void st_release(int* p, int v)
-{
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
 __device__ __forceinline__ const SegDesc& find_seg(const Pipe& p, const FrameDesc& fr, int i)
 {
@@ -193,7 +156,7 @@ __device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int
 {
     if (fr.pts0) {
         if (p.vec4) {
-            const float4 v = __ldg(reinterpret_cast<const float4*>(fr.pts0) + i);
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(fr.pts0) + i);  // streamed once
             x = v.x; y = v.y; z = v.z;
         } else {
             const float* q = fr.pts0 + (size_t)i * p.f_in;
@@ -204,7 +167,7 @@ __device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int
     const SegDesc& sg = find_seg(p, fr, i);
     const float* q = sg.pts + (size_t)(i - sg.start) * p.f_in;
     if (p.vec4) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(q));
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(q));
         x = v.x; y = v.y; z = v.z;
     } else {
         x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
@@ -239,6 +202,121 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
     dst[0] = x; dst[1] = y; dst[2] = z;
 }
 
+// ---------------------------------------------------------------- k_insert
+// grid (B, max chunks per frame): x = frame, so blocks are dispatched chunk-row by
+// chunk-row across all frames.  A block takes the frame's next chunk in index order
+// from a ticket counter.  Thread t of chunk c owns points c*1024 + k*256 + t,
+// k = 0..3: every warp-wide access is coalesced and a warp covers exactly one
+// 32-point mask word per k.
+//
+// Break early exit (the reference's serial loop stops at the point that would open
+// voxel #cap): before taking its ticket a block reads the number of distinct cells
+// claimed by finished chunks.  If that already exceeds cap, every point that was
+// inserted lies in a chunk with a smaller ticket, so the cut-off index i* lies
+// before this chunk and the chunk is skipped (nothing it holds can be kept).
+// Skipping is monotone, so the inserted points always form a prefix [0, n_eff).
+//
+// Table protocol, CAS first, in ROUNDS (one atomic per point in flight, 4 per
+// thread -- the kernel is bound by L2 atomic round trips, tools/microbench2.cu):
+//   atomicCAS(empty -> {cell, i}):  was empty   -> new cell, I am a candidate
+//                                   same cell   -> atomicMin if my index is smaller
+//                                   other cell  -> probe the next slot
+__global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
+{
+    __shared__ int s_chunk;
+    __shared__ int s_new[kWarps];
+    const int f = blockIdx.x;
+    const FrameDesc fr = p.frames[f];
+    if ((int)blockIdx.y * kChunk >= fr.n) return;
+    FrameState* st = p.state + f;
+    if (threadIdx.x == 0) {
+        const int d = __ldcg(&st->distinct);           // read BEFORE the ticket (see above)
+        __threadfence();                               // ... and ordered before it
+        int c = atomicAdd(&st->next_chunk, 1);
+        if (!p.overflow_continue && d > p.cap && c * kChunk < fr.n) {
+            atomicMin(&st->n_eff, c * kChunk);
+            c = 0x7FFFFFF;                             // skipped
+        }
+        s_chunk = c;
+    }
+    __syncthreads();
+    const long long basel = (long long)s_chunk * kChunk;
+    if (basel >= fr.n) return;
+    const int base = (int)basel;
+    unsigned long long* tbl = p.table + fr.tbl_off;
+    int cell[kPts];
+    unsigned int h[kPts];
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        cell[k] = -1;
+        if (i < fr.n) {
+            float x, y, z;
+            load_xyz(p, fr, i, x, y, z);
+            cell[k] = cell_of(p.g, x, y, z);
+        }
+    }
+    unsigned int active = 0, needmin = 0, wonmask = 0, newmask = 0;
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        h[k] = 0;
+        if (cell[k] >= 0) {
+            h[k] = fr.tbl_shift < 0 ? (unsigned)cell[k] : hash_cell((unsigned)cell[k], fr.tbl_shift);
+            active |= 1u << k;
+        }
+    }
+    while (active) {
+        unsigned long long r[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const unsigned long long mine = ((unsigned long long)(unsigned)cell[k] << 32) |
+                                            (unsigned)(base + k * kBlock + threadIdx.x);
+            r[k] = 0;
+            if (active & (1u << k))
+                r[k] = (needmin & (1u << k)) ? atomicMin(tbl + h[k], mine)
+                                             : atomicCAS(tbl + h[k], kEmpty64, mine);
+        }
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const unsigned int bit = 1u << k;
+            if (!(active & bit)) continue;
+            const unsigned int i = (unsigned)(base + k * kBlock + threadIdx.x);
+            if (needmin & bit) {
+                if ((unsigned)r[k] > i) wonmask |= bit;
+                active &= ~bit;
+            } else if (r[k] == kEmpty64) {
+                wonmask |= bit; newmask |= bit; active &= ~bit;
+            } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
+                if ((unsigned)r[k] > i) needmin |= bit; else active &= ~bit;
+            } else {
+                h[k] = (h[k] + 1) & fr.tbl_mask;
+            }
+        }
+    }
+    int nnew = 0;
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        if (i < fr.n) p.slot[fr.pt_off + i] = cell[k] >= 0 ? (int)h[k] : -1;
+        const unsigned int b = __ballot_sync(0xffffffffu, (wonmask >> k) & 1u);
+        nnew += __popc(__ballot_sync(0xffffffffu, (newmask >> k) & 1u));
+        const int w = i >> 5;
+        if ((threadIdx.x & 31) == 0 && w < fr.nwords) p.cand[fr.word_off + w] = b;
+    }
+    if (!p.overflow_continue) {
+        // publish the cells this chunk claimed; later tickets read it before they start
+        if ((threadIdx.x & 31) == 0) s_new[threadIdx.x >> 5] = nnew;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) t += s_new[w];
+            if (t) atomicAdd(&st->distinct, t);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- k_verify
 __device__ __forceinline__ int warp_exclusive_scan(int v, int lane, int* total)
 {
     int inc = v;
@@ -251,18 +329,7 @@ __device__ __forceinline__ int warp_exclusive_scan(int v, int lane, int* total)
     return inc - v;
 }
 
-// ---------------------------------------------------------------- k_chain
-struct ChainSmem {
-    unsigned int lkey[kLSlots];    // cell of the local slot; after the chain: slot base of the cell's voxel
-    unsigned int lhead[kLSlots];   // newest point (local index) of the slot's list; after the chain: voxel id
-    unsigned short lnext[kCChunk]; // next older list member
-    int wcnt[kCP * kCWarps];       // new voxels per (k, warp), then their exclusive prefix
-    int s_g, s_done, s_nvox, s_total, s_istar, s_last;
-};
-static_assert((kCP * kCWarps) % 32 == 0 && (kCP * kCWarps) / 32 <= 8, "scan shape");
-
-template <int NT>
-__device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem /*[NT/32]*/)
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem /*[kWarps+1]*/)
 {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     int wt;
@@ -272,7 +339,7 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem
     __syncthreads();
     int base = 0, tot = 0;
 #pragma unroll
-    for (int k = 0; k < NT / 32; ++k) {
+    for (int k = 0; k < kWarps; ++k) {
         const int s = smem[k];
         if (k < wid) base += s;
         tot += s;
@@ -281,323 +348,250 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem
     return base + ex;
 }
 
-// Wait until the frame's chain counter reaches `want` chunks (or the frame is closed).
-__device__ __forceinline__ int chain_wait(const int* done, int want)
+// Frame-level part, run by the last chunk of the frame to finish k_verify: scan the
+// chunk counts in place (chunkbase becomes the exclusive prefix), publish total / M /
+// i*, and -- for the last frame of the call -- the exclusive prefix of M over frames.
+__device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, int* sm)
 {
-    int d;
-    for (;;) {
-        d = ld_acquire(done);
-        if ((d & kClosedBit) || d >= want) break;
-        __nanosleep(20);
+    const int nchunks = (eff + kChunk - 1) / kChunk, nwords = (eff + 31) / 32;
+    int* cb = p.chunkbase + fr.chunk_off;
+    const int cap = p.cap;
+    int carry = 0;
+    int cut_chunk = -1, cut_base = 0;
+    for (int b0 = 0; b0 < nchunks; b0 += kBlock) {
+        const int c = b0 + threadIdx.x;
+        const int v = c < nchunks ? __ldcg(cb + c) : 0;
+        int tot;
+        const int ex = carry + block_exclusive_scan(v, &tot, sm);
+        if (c < nchunks) {
+            cb[c] = ex;
+            if (ex <= cap && cap < ex + v) { cut_chunk = c; cut_base = ex; }  // at most one thread
+        }
+        carry += tot;
     }
-    return d;
+    const int total = carry;
+    const bool cut = (!p.overflow_continue) && total > cap;
+    if (threadIdx.x == 0) {
+        p.state[f].total = total;
+        p.state[f].m = min(total, cap);
+        p.state[f].done_verify = 0;            // ready for the next call
+        p.state[f].n_done = eff;
+        if (!cut) p.state[f].istar = eff;
+    }
+    if (cut && cut_chunk >= 0) {
+        // the point that would open voxel #cap: (cap - prefix)-th first occurrence of this chunk
+        int need = cap - cut_base;
+        const int w0 = fr.word_off + cut_chunk * kChunkWords;
+        const int nw = min(kChunkWords, nwords - cut_chunk * kChunkWords);
+        int w = 0;
+        for (; w + 1 < nw; ++w)
+            if (__ldcg(p.wordlocal + w0 + w + 1) > need) break;
+        need -= __ldcg(p.wordlocal + w0 + w);
+        unsigned int m = __ldcg(p.first + w0 + w);
+        for (; need > 0; --need) m &= m - 1;
+        p.state[f].istar = (cut_chunk * kChunkWords + w) * 32 + (__ffs(m) - 1);
+    }
+    __threadfence();
+    __syncthreads();
+    __shared__ int s_lastframe;
+    if (threadIdx.x == 0) s_lastframe = (atomicAdd(&p.counters[0], 1) == p.nframes - 1);
+    __syncthreads();
+    if (!s_lastframe) return;
+    __threadfence();
+    carry = 0;
+    for (int b0 = 0; b0 < p.nframes; b0 += kBlock) {
+        const int ff = b0 + threadIdx.x;
+        const int m = ff < p.nframes ? __ldcg(&p.state[ff].m) : 0;
+        int tot;
+        const int ex = block_exclusive_scan(m, &tot, sm);
+        if (ff < p.nframes) p.frame_voxel_offsets[ff] = carry + ex;
+        carry += tot;
+    }
+    if (threadIdx.x == 0) {
+        p.frame_voxel_offsets[p.nframes] = carry;
+        p.counters[0] = 0;
+        p.counters[1] = 0;
+    }
 }
 
-// grid: persistent, block kCT; dynamic smem sizeof(ChainSmem).
-// Ticket g -> (row r = g / B, frame f = g % B): chunk r of frame f.  A frame's chunks
-// are ticketed in increasing order, so the block that holds chunk r-1 is always
-// already running when chunk r waits for it (no deadlock, any grid size).
-__global__ void __launch_bounds__(kCT, kCT >= 1024 ? 1 : 2) k_chain(const Pipe p)
+// grid (max chunks per frame, B); same point mapping as k_insert.
+__global__ void __launch_bounds__(kBlock) k_verify(const Pipe p)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    ChainSmem& sm = *reinterpret_cast<ChainSmem*>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int T = p.T, cap = p.cap;
-    const int ntickets = p.rows * p.nframes;
-    for (;;) {
-        __syncthreads();                       // previous ticket is done with shared memory
-        if (tid == 0) {
-            int g = atomicAdd(&p.counters[0], 1);
-            if (g < ntickets && ld_acquire(&p.counters[2])) g = ntickets;   // every frame is complete
-            sm.s_g = g;
-            // a frame whose cut-off is already known needs none of its later chunks
-            sm.s_done = g < ntickets ? ld_acquire(&p.state[g % p.nframes].done) : 0;
-        }
-        {   // clear the local table while the ticket is in flight
-            uint4* c4 = reinterpret_cast<uint4*>(sm.lkey);
-            const uint4 e = make_uint4(kEmpty32, kEmpty32, kEmpty32, kEmpty32);
+    __shared__ unsigned int s_first[kChunkWords];
+    __shared__ int sm[kWarps + 1];
+    __shared__ int s_last;
+    const int f = blockIdx.y;
+    const FrameDesc fr = p.frames[f];
+    const int base = blockIdx.x * kChunk;
+    const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));   // prefix that went through k_insert
+    if (base >= eff && !(eff == 0 && blockIdx.x == 0)) return;
+    const int nwords = (eff + 31) / 32;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned long long* tbl = p.table + fr.tbl_off;
+    if (eff > 0) {
+        int sl[kPts];
+        bool cd[kPts];
 #pragma unroll
-            for (int k = 0; k < (2 * kLSlots / 4) / kCT; ++k) c4[k * kCT + tid] = e;
+        for (int k = 0; k < kPts; ++k) {
+            const int i = base + k * kBlock + threadIdx.x;
+            const int w = i >> 5;
+            const unsigned int cw = w < nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
+            cd[k] = (cw >> lane) & 1u;
+            sl[k] = cd[k] ? __ldg(p.slot + fr.pt_off + i) : 0;
+        }
+        unsigned long long e[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) e[k] = cd[k] ? __ldcg(tbl + sl[k]) : 0ull;
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            const int i = base + k * kBlock + threadIdx.x;
+            const bool isf = cd[k] && (unsigned)e[k] == (unsigned)i;
+            const unsigned int b = __ballot_sync(0xffffffffu, isf);
+            if (lane == 0) s_first[k * kWarps + wid] = b;
         }
         __syncthreads();
-        const int g = sm.s_g;
-        if (g >= ntickets) break;
-        const int f = g % p.nframes, r = g / p.nframes;
-        const FrameDesc fr = p.frames[f];
-        const int base = r * kCChunk;
-        if ((base >= fr.n && r > 0) || (sm.s_done & kClosedBit)) continue;
-        FrameState* st = p.state + f;
-        BVX_TRACE(0);
+        if (wid == 0) {
+            const unsigned int fw = s_first[lane];
+            int tot;
+            const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
+            const int w = blockIdx.x * kChunkWords + lane;
+            if (w < nwords) {
+                p.first[fr.word_off + w] = fw;
+                p.wordlocal[fr.word_off + w] = ex;
+            }
+            if (lane == 0) p.chunkbase[fr.chunk_off + blockIdx.x] = tot;
+        }
+    }
+    // last chunk of the frame -> frame-level scan
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+        s_last = (atomicAdd(&p.state[f].done_verify, 1) == max((eff + kChunk - 1) / kChunk, 1) - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    frame_scan(p, fr, f, eff, sm);
+}
 
-        // ---- phase 1: cell keys (coalesced: thread t owns points base + k*kCT + t)
-        int cell[kCP];
+// ---------------------------------------------------------------- k_slot
+// grid (gx, B): block x of frame f walks chunks x, x+gx, ... below the break
+// cut-off, so the launch carries no blocks that only exit.  Same round structure as
+// k_insert: per round one atomic per point in flight.
+__global__ void __launch_bounds__(kBlock) k_slot(const Pipe p)
+{
+    const int f = blockIdx.y;
+    const FrameDesc fr = p.frames[f];
+    const int lim = min(p.state[f].n_done, p.state[f].istar);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // k_insert's per-frame counters, for the next call
+        p.state[f].next_chunk = 0;
+        p.state[f].distinct = 0;
+        p.state[f].n_eff = 0x7FFFFFFF;
+    }
+    const unsigned long long* tbl = p.table + fr.tbl_off;
+    const int T = p.T;
+    for (int base = blockIdx.x * kChunk; base < lim; base += gridDim.x * kChunk) {
+        int sl[kPts];
 #pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            const int i = base + k * kCT + tid;
-            cell[k] = -1;
-            if (i < fr.n) {
-                float x, y, z;
-                load_xyz(p, fr, i, x, y, z);
-                cell[k] = cell_of(p.g, x, y, z);
+        for (int k = 0; k < kPts; ++k) {
+            const int i = base + k * kBlock + threadIdx.x;
+            sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;
+        }
+        unsigned long long e[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) e[k] = sl[k] >= 0 ? __ldcg(tbl + sl[k]) : 0ull;
+        int rank[kPts];
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            rank[k] = 0x7FFFFFFF;
+            if (sl[k] >= 0) {
+                const unsigned int fidx = (unsigned)e[k];
+                const int w = fidx >> 5;
+                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
+                          __ldg(p.wordlocal + fr.word_off + w) +
+                          __popc(__ldg(p.first + fr.word_off + w) & ((1u << (fidx & 31)) - 1u));
             }
         }
-        // ---- phase 2: the chunk's distinct cells (shared-memory hash) + per-cell point lists
-        unsigned int pk[kCP];                  // local slot | (rank or multiplicity) << 16
+        // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
+        if (T <= kChainMaxT) {
+            // sorted insertion: slot j ends up holding the (j+1)-th smallest index offered
+            int cur[kPts];
+            int* b[kPts];
+            unsigned int active = 0;
 #pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            pk[k] = 0;
-            if (cell[k] >= 0) {
-                unsigned int h = hash_cell((unsigned)cell[k], kLShift);
-                for (;;) {
-                    const unsigned int old = atomicCAS(&sm.lkey[h], kEmpty32, (unsigned)cell[k]);
-                    if (old == kEmpty32 || old == (unsigned)cell[k]) break;
-                    h = (h + 1) & (kLSlots - 1);
-                }
-                const unsigned int li = k * kCT + tid;
-                const unsigned int prev = atomicExch(&sm.lhead[h], li);
-                sm.lnext[li] = (unsigned short)prev;       // kEmpty32 -> kLEnd
-                pk[k] = h;
+            for (int k = 0; k < kPts; ++k) {
+                cur[k] = base + k * kBlock + threadIdx.x;
+                b[k] = p.bucket + ((size_t)f * p.cap + (rank[k] < p.cap ? rank[k] : 0)) * T;
+                if (rank[k] < p.cap) active |= 1u << k;
             }
-        }
-        __syncthreads();
-        // ---- phase 3: input-order rank of every point among the chunk's points of its cell
-        unsigned int firstmask = 0;
+            for (int j = 0; j < T && active; ++j) {
+                int old[kPts];
 #pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            if (cell[k] >= 0) {
-                const unsigned int li = k * kCT + tid;
-                unsigned int j = sm.lhead[pk[k]];
-                unsigned int smaller = 0, total = 0;
-                while (j != kLEnd) {
-                    ++total;
-                    smaller += (j < li);
-                    j = sm.lnext[j];
-                }
-                if (smaller == 0) { firstmask |= 1u << k; pk[k] |= total << 16; }
-                else pk[k] |= smaller << 16;
-            }
-        }
-        BVX_TRACE(1);
-        // ---- phase 4: when the chain is one chunk away, probe the frame's table (plain loads):
-        // where does each distinct cell live, or which empty slot would it take?
-        Entry* tbl = p.table + fr.tbl_off;
-        unsigned int gh[kCP];
-        int nvid[kCP];                         // voxel id when the probe already saw it (-1 unknown)
-        unsigned int foundmask = 0;
-        {
-            if (r > 1 && lane == 0) chain_wait(&st->done, r - 1);
-            __syncwarp();
-            unsigned int unres = firstmask;
+                for (int k = 0; k < kPts; ++k)
+                    old[k] = (active & (1u << k)) ? atomicMin(b[k] + j, cur[k]) : 0;
 #pragma unroll
-            for (int k = 0; k < kCP; ++k) {
-                nvid[k] = kVidUnset;
-                gh[k] = fr.tbl_shift < 0 ? (unsigned)cell[k] : hash_cell((unsigned)cell[k], fr.tbl_shift);
-            }
-            while (unres) {
-#pragma unroll
-                for (int k0 = 0; k0 < kCP; k0 += 4) {      // four probes in flight per step (registers)
-                    uint4 e[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (unres & (1u << (k0 + q))) e[q] = __ldcg(reinterpret_cast<const uint4*>(tbl + gh[k0 + q]));
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int k = k0 + q;
-                        const unsigned int bit = 1u << k;
-                        if (!(unres & bit)) continue;
-                        if (e[q].y == (unsigned)cell[k]) { foundmask |= bit; nvid[k] = (int)e[q].z; unres &= ~bit; }
-                        else if (e[q].y == kEmpty32) unres &= ~bit;
-                        else gh[k] = (gh[k] + 1) & fr.tbl_mask;
+                for (int k = 0; k < kPts; ++k) {
+                    if (active & (1u << k)) {
+                        if (old[k] == kEmptyIdx) active &= ~(1u << k);
+                        else cur[k] = max(old[k], cur[k]);
                     }
                 }
             }
-        }
-        // ---- phase 5: my turn on the chain
-        int d = 0, nvox0 = 0;
-        if (r > 0) {
-            if (lane == 0) { d = chain_wait(&st->done, r); nvox0 = __ldcg(&st->nvox); }
-            d = __shfl_sync(0xffffffffu, d, 0);
-            nvox0 = __shfl_sync(0xffffffffu, nvox0, 0);
-        }
-        if (d & kClosedBit) continue;          // the break cut-off lies before this chunk (block-uniform)
-        BVX_TRACE(2);
-        const bool full = nvox0 >= cap;        // table is frozen: never insert
-        // one atomic per distinct cell claims the cell (if new) AND reserves the slots of
-        // all its points in this chunk: key = {cell:32 | points offered so far:32}
-        unsigned int unres = firstmask, newmask = 0, missmask = 0;
-        while (unres) {
-            unsigned long long rr[kCP];
+        } else {
 #pragma unroll
-            for (int k = 0; k < kCP; ++k) {
-                const unsigned int bit = 1u << k;
-                if (!(unres & bit)) continue;
-                const unsigned long long m = (pk[k] >> 16);
-                if (foundmask & bit) rr[k] = atomicAdd(&tbl[gh[k]].key, m);
-                else if (full) rr[k] = __ldcg(&tbl[gh[k]].key);
-                else rr[k] = atomicCAS(&tbl[gh[k]].key, kEmpty64, ((unsigned long long)(unsigned)cell[k] << 32) | m);
-            }
-#pragma unroll
-            for (int k = 0; k < kCP; ++k) {
-                const unsigned int bit = 1u << k;
-                if (!(unres & bit)) continue;
-                if (foundmask & bit) { cell[k] = (int)(unsigned)rr[k]; unres &= ~bit; }        // slot base
-                else if (rr[k] == kEmpty64) {
-                    if (full) missmask |= bit; else newmask |= bit;
-                    cell[k] = 0; unres &= ~bit;
+            for (int k = 0; k < kPts; ++k) {
+                if (rank[k] >= p.cap) continue;
+                const int i = base + k * kBlock + threadIdx.x;
+                const size_t g = (size_t)f * p.cap + rank[k];
+                const int c = atomicAdd(p.cnt + g, 1);
+                if (c < T) {
+                    p.bucket[g * T + c] = i;
+                } else {
+                    const int o = atomicAdd(&p.counters[1], 1);
+                    if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
                 }
-                else if ((unsigned)(rr[k] >> 32) == (unsigned)cell[k]) foundmask |= bit;       // came in since the probe
-                else gh[k] = (gh[k] + 1) & fr.tbl_mask;
             }
         }
-        // from here cell[k] of a first point holds the slot base of its cell
-        BVX_TRACE(3);
-        // ---- phase 6: count the new voxels and hand the chain on
-        const unsigned int cntmask = newmask | missmask;   // break + full: a miss is the cut-off point
-#pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            const unsigned int b = __ballot_sync(0xffffffffu, (cntmask >> k) & 1u);
-            if (lane == 0) sm.wcnt[k * kCWarps + warp] = __popc(b);
-        }
-        __syncthreads();
-        if (warp == 0) {
-            constexpr int per = kCP * kCWarps / 32;
-            int v[per], s = 0;
-#pragma unroll
-            for (int q = 0; q < per; ++q) { v[q] = sm.wcnt[lane * per + q]; s += v[q]; }
-            int tot;
-            int ex = warp_exclusive_scan(s, lane, &tot);
-            if (lane == 0) {
-                const bool over0 = nvox0 + tot > cap;
-                const bool cut0 = over0 && !p.overflow_continue;
-                const bool lastchunk = (long long)base + kCChunk >= fr.n;
-                const int nv1 = over0 ? cap : nvox0 + tot;
-                st->nvox = nv1;
-                if (over0 && !full) st->ndead = nvox0 + tot - cap;
-                if (cut0 || lastchunk) st->m = nv1;
-                st_release(&st->done, (r + 1) | (cut0 ? kClosedBit : 0));   // hand the chain on
-                if (p.trace) p.trace[(size_t)g * 8 + 5] = gtime();
-                sm.s_total = tot;
-                int last = 0;
-                if (cut0 || lastchunk) {
-                    __threadfence();
-                    last = (atomicAdd(&p.counters[1], 1) == p.nframes - 1);
-                }
-                sm.s_last = last;
-                sm.s_istar = 0x7FFFFFFF;
-            }
-#pragma unroll
-            for (int q = 0; q < per; ++q) { sm.wcnt[lane * per + q] = ex; ex += v[q]; }
-        }
-        __syncthreads();
-        // ---- off the chain: number the new voxels in input order
-        const int total_new = sm.s_total;
-        const bool over = nvox0 + total_new > cap;
-        const bool cut = over && !p.overflow_continue;
-#pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            const unsigned int bit = 1u << k;
-            const unsigned int b = __ballot_sync(0xffffffffu, (cntmask >> k) & 1u);
-            if (!(cntmask & bit)) continue;
-            const int vid = nvox0 + sm.wcnt[k * kCWarps + warp] + __popc(b & ((1u << lane) - 1u));
-            if (cut && vid == cap) sm.s_istar = base + k * kCT + tid;   // the point that would open voxel #cap
-            if (missmask & bit) { nvid[k] = kVidDead; continue; }
-            if (vid < cap) {
-                tbl[gh[k]].vid = vid;
-                p.vslot[(size_t)f * cap + vid] = gh[k];
-                nvid[k] = vid;
-            } else {       // claimed beyond the cap: dead; remember the slot for the reset
-                tbl[gh[k]].vid = kVidDead;
-                p.dead[(size_t)f * kCChunk + (vid - cap)] = gh[k];
-                nvid[k] = kVidDead;
-            }
-        }
-        BVX_TRACE(4);
-        if (cut) __syncthreads();
-        const int istar = cut ? sm.s_istar : 0x7FFFFFFF;
-        // per-cell voxel id / slot base for the other points of the cell
-#pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            const unsigned int bit = 1u << k;
-            if (!(firstmask & bit)) continue;
-            const unsigned int lh = pk[k] & 0xFFFFu;
-            int vid = nvid[k];
-            if (vid == kVidUnset) {            // created by a recent chunk: its number is on its way
-                const int* vp = &tbl[gh[k]].vid;
-                while ((vid = __ldcg(vp)) == kVidUnset) __nanosleep(20);
-            }
-            if (cut && vid >= 0) {             // only points before the cut-off count: give the rest back
-                int keep = 0;
-                unsigned int j = sm.lhead[lh];
-                while (j != kLEnd) { keep += (base + (int)j < istar); j = sm.lnext[j]; }
-                const int m = (int)(pk[k] >> 16);
-                if (keep < m) atomicAdd(&tbl[gh[k]].key, (unsigned long long)(long long)(keep - m));
-            }
-            nvid[k] = vid;
-        }
-        __syncthreads();                       // all list walks done before the lists are overwritten
-#pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            if (firstmask & (1u << k)) {
-                const unsigned int lh = pk[k] & 0xFFFFu;
-                sm.lhead[lh] = (unsigned)nvid[k];
-                sm.lkey[lh] = (unsigned)cell[k];
-            }
-        }
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < kCP; ++k) {
-            const int i = base + k * kCT + tid;
-            const unsigned int lh = pk[k] & 0xFFFFu;
-            const bool first = (firstmask >> k) & 1u;
-            const unsigned int rk = first ? 0u : (pk[k] >> 16);
-            const bool took = first || rk > 0;      // non-first points always have rank >= 1
-            if (!took || i >= istar) continue;
-            const int vid = (int)sm.lhead[lh];
-            if (vid < 0) continue;
-            const unsigned int slot = sm.lkey[lh] + rk;
-            if (slot < (unsigned)T) p.bucket[((size_t)f * cap + vid) * T + slot] = i;
-        }
-        BVX_TRACE(6);
-        if (sm.s_last) {
-            // every frame is complete: exclusive prefix of M over frames
-            __threadfence();
-            int carry = 0;
-            for (int b0 = 0; b0 < p.nframes; b0 += kCT) {
-                const int ff = b0 + tid;
-                const int m = ff < p.nframes ? __ldcg(&p.state[ff].m) : 0;
-                int tot;
-                const int ex = block_exclusive_scan<kCT>(m, &tot, sm.wcnt);
-                if (ff < p.nframes) p.frame_voxel_offsets[ff] = carry + ex;
-                carry += tot;
-            }
-            if (tid == 0) {
-                p.frame_voxel_offsets[p.nframes] = carry;
-                p.counters[1] = 0;
-                __threadfence();
-                st_release(&p.counters[2], 1);
-            }
+    }
+}
+
+// ---------------------------------------------------------------- k_overflow
+// Large-T path: a crowded voxel's bucket holds T arbitrary members; every other
+// member is offered here and the bucket keeps the T smallest indices.
+__global__ void __launch_bounds__(kBlock) k_overflow(const Pipe p)
+{
+    const int n = min(((volatile int*)p.counters)[1], p.ovf_cap);
+    for (int j = blockIdx.x * kBlock + threadIdx.x; j < n; j += gridDim.x * kBlock) {
+        const int2 it = p.ovf[j];
+        int* b = p.bucket + (size_t)it.x * p.T;
+        int mx = 0;
+        for (int k = 0; k < p.T; ++k) mx = max(mx, __ldcg(b + k));
+        if (it.y > mx) continue;  // entries only decrease: cannot be among the T smallest
+        int cur = it.y;
+        for (int k = 0; k < p.T; ++k) {
+            const int old = atomicMin(b + k, cur);
+            cur = max(old, cur);
         }
     }
 }
 
 // ---------------------------------------------------------------- k_gather
-__device__ __forceinline__ void reset_entry(Entry* e)
+// Table reset, shared by both gather kernels: blocks past the voxel tiles walk the
+// frame's chunks and clear the slot of every candidate (a superset of the entries
+// the frame created), so the next call starts from an empty table without a memset.
+__device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, int chunk)
 {
-    *reinterpret_cast<uint4*>(e) = make_uint4(kEmpty32, kEmpty32, (unsigned)kVidUnset, 0u);
-}
-
-// Block 0 of every frame returns the chain state to its clean state for the next
-// call: dead-cell table entries, the frame's chain words, the call-wide counters.
-__device__ __forceinline__ void housekeeping(const Pipe& p, const FrameDesc& fr, int f)
-{
-    FrameState* st = p.state + f;
-    const int nd = st->ndead;
-    Entry* tbl = p.table + fr.tbl_off;
-    for (int j = threadIdx.x; j < nd; j += blockDim.x) reset_entry(tbl + p.dead[(size_t)f * kCChunk + j]);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        st->done = 0; st->nvox = 0; st->istar = 0x7FFFFFFF; st->ndead = 0;
-        if (f == 0) { p.counters[0] = 0; p.counters[2] = 0; }
+    const int base = chunk * kChunk;
+    const int eff = p.state[blockIdx.y].n_done;
+    if (base >= eff) return;
+    const int nwords = (eff + 31) / 32;
+    const int lane = threadIdx.x & 31;
+    unsigned long long* tbl = p.table + fr.tbl_off;
+#pragma unroll
+    for (int k = 0; k < kPts; ++k) {
+        const int i = base + k * kBlock + threadIdx.x;
+        const int w = i >> 5;
+        const unsigned int cw = w < nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
+        if ((cw >> lane) & 1u) tbl[__ldg(p.slot + fr.pt_off + i)] = kEmpty64;
     }
 }
 
@@ -614,43 +608,41 @@ __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int 
     }
 }
 
-// Fast path: T <= 8, 4 floats per point, 16-byte aligned rows, plain frames.  One
-// thread per voxel: its table entry gives the cell (-> coordinates) and the number
-// of points offered (-> num_points); T independent row loads in flight; the voxel
-// rows go through a per-warp shared-memory transpose so the [M, T, 4] store is
-// fully coalesced.  grid (tiles, B); dynamic smem = kWarps * 32 * T * 16 bytes.
+// Fast path: T <= 8 (bucket already sorted by the atomicMin chain), 4 floats per
+// point, 16-byte aligned rows.  One thread per voxel: T independent row loads in
+// flight, mean and coordinates from registers; the voxel rows go through a
+// per-warp shared-memory transpose so the [M, T, 4] store is fully coalesced.
+// grid (tiles + reset chunks, B); dynamic smem = kWarps * 32 * T * 16 bytes.
 template <int T>
-__global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p)
+__global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles)
 {
     extern __shared__ float4 smem_v[];
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
+    if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * kBlock;
-    if (blockIdx.x == 0) housekeeping(p, fr, f);
     if (v0 >= mf) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int v = v0 + threadIdx.x;
     const bool live = v < mf;
     const size_t gbase = (size_t)p.frame_voxel_offsets[f];
-    const size_t fv = (size_t)f * p.cap + v;
-    int nvalid = 0, cell = 0;
-    if (live) {
-        Entry* e = p.table + fr.tbl_off + __ldcs(p.vslot + fv);
-        const uint4 ev = __ldcg(reinterpret_cast<const uint4*>(e));
-        nvalid = (int)min(ev.x, (unsigned)T);
-        cell = (int)ev.y;
-        reset_entry(e);                             // workspace back to clean
-    }
     int idx[T];
-    const int* gb = p.bucket + fv * T;
+    int* gb = p.bucket + ((size_t)f * p.cap + v) * T;
 #pragma unroll
-    for (int s = 0; s < T; ++s) idx[s] = s < nvalid ? __ldcs(gb + s) : -1;
+    for (int s = 0; s < T; ++s) {
+        idx[s] = live ? gb[s] : kEmptyIdx;
+        if (live) gb[s] = kEmptyIdx;
+    }
     float4 row[T];
+    int nvalid = 0;
 #pragma unroll
     for (int s = 0; s < T; ++s) {
         row[s] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (idx[s] >= 0) row[s] = __ldg(reinterpret_cast<const float4*>(fr.pts0) + idx[s]);
+        if (idx[s] != kEmptyIdx) {
+            row[s] = __ldg(reinterpret_cast<const float4*>(fr.pts0) + idx[s]);
+            ++nvalid;
+        }
     }
     // per-warp transpose: voxel-major float4 index lane*T + s, read back linearly
     float4* sw = smem_v + wid * (32 * T);
@@ -674,7 +666,7 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p)
     if (!live) return;
     const size_t gv = gbase + v;
     p.num_points[gv] = nvalid;
-    write_coor(p, f, gv, cell);
+    write_coor(p, f, gv, cell_of(p.g, row[0].x, row[0].y, row[0].z));
     if (p.mean_out) {
         float sx = 0.f, sy = 0.f, sz = 0.f, swt = 0.f;
 #pragma unroll
@@ -693,43 +685,52 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p)
 }
 
 // General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T bucket
-// entries) staged through shared memory.
-// grid (tiles, B); dynamic smem: round4(vt) ints + vt*T*f_out floats.
-__global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int vt)
+// entries) staged through shared memory; entries are rank-sorted in shared memory
+// (the large-T bucket is unordered).
+// grid (tiles + reset chunks, B); dynamic smem: round4(E) ints + E*f_out floats, E = vt*T.
+__global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int vt)
 {
     extern __shared__ int smem_i[];
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
+    if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * vt;
-    if (blockIdx.x == 0) housekeeping(p, fr, f);
     if (v0 >= mf) return;
     const int T = p.T, F = p.f_out;
     const int nv = min(vt, mf - v0);
     const int E = nv * T;
-    int* scnt = smem_i;
-    float* srow = reinterpret_cast<float*>(smem_i + ((vt + 3) & ~3));
-    const size_t fv0 = (size_t)f * p.cap + v0;
-    const size_t gout = (size_t)p.frame_voxel_offsets[f] + v0;
-    for (int v = threadIdx.x; v < nv; v += kBlock) {
-        Entry* e = p.table + fr.tbl_off + __ldcs(p.vslot + fv0 + v);
-        const uint4 ev = __ldcg(reinterpret_cast<const uint4*>(e));
-        const int c = (int)min(ev.x, (unsigned)T);
-        scnt[v] = c;
-        reset_entry(e);
-        p.num_points[gout + v] = c;
-        write_coor(p, f, gout + v, (int)ev.y);
+    int* sidx = smem_i;
+    float* srow = reinterpret_cast<float*>(smem_i + ((vt * T + 3) & ~3));
+    int* gb = p.bucket + ((size_t)f * p.cap + v0) * T;
+    for (int e = threadIdx.x; e < E; e += kBlock) {
+        sidx[e] = gb[e];
+        gb[e] = kEmptyIdx;
     }
+    if (T > kChainMaxT)
+        for (int v = threadIdx.x; v < nv; v += kBlock) p.cnt[(size_t)f * p.cap + v0 + v] = 0;
     __syncthreads();
-    const int* gb = p.bucket + fv0 * T;
+    const size_t gout = (size_t)p.frame_voxel_offsets[f] + v0;
     for (int e = threadIdx.x; e < E; e += kBlock) {
         const int v = e / T, s = e - v * T;
-        float* dst = srow + (size_t)e * F;
-        if (s < scnt[v]) {
-            fetch_row(p, fr, __ldcs(gb + e), dst);
-        } else {
-            for (int k = 0; k < F; ++k) dst[k] = 0.0f;
+        const int my = sidx[e];
+        const int* vb = sidx + v * T;
+        int nvalid = 0, r = 0;
+        for (int k = 0; k < T; ++k) {
+            const int o = vb[k];
+            nvalid += (o != kEmptyIdx);
+            r += (o < my);
         }
+        if (my != kEmptyIdx) {
+            float* dst = srow + (size_t)(v * T + r) * F;
+            fetch_row(p, fr, my, dst);
+            if (r == 0) write_coor(p, f, gout + v, cell_of(p.g, dst[0], dst[1], dst[2]));
+        }
+        if (s >= nvalid) {
+            float* z = srow + (size_t)(v * T + s) * F;
+            for (int k = 0; k < F; ++k) z[k] = 0.0f;
+        }
+        if (s == 0) p.num_points[gout + v] = nvalid;
     }
     __syncthreads();
     float* out = p.voxels + gout * T * F;
@@ -745,9 +746,12 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int vt)
         const int C = p.mean_c;
         for (int k = threadIdx.x; k < nv * C; k += kBlock) {
             const int v = k / C, c = k - v * C;
+            const int* vb = sidx + v * T;
+            int nvalid = 0;
+            for (int j = 0; j < T; ++j) nvalid += (vb[j] != kEmptyIdx);
             float s = 0.0f;
             for (int j = 0; j < T; ++j) s = __fadd_rn(s, srow[(size_t)(v * T + j) * F + c]);
-            p.mean_out[(gout + v) * C + c] = __fdiv_rn(s, (float)scnt[v]);
+            p.mean_out[(gout + v) * C + c] = __fdiv_rn(s, (float)nvalid);
         }
     }
 }

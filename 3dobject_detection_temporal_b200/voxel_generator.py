@@ -156,24 +156,6 @@ class VoxelGenerator:
         return {_lib.KERNEL_NAMES[i]: (float(ms[i]), int(n[i])) for i in range(_lib.PROFILE_SLOTS)
                 if _lib.KERNEL_NAMES[i] and n[i] > 0}
 
-    def chain_trace(self, max_tickets=None):
-        """Diagnostics: ``chain_trace(n)`` arms per-ticket phase stamps of k_chain for
-        calls of up to n chunk tickets; ``chain_trace()`` returns the last call's
-        ``(stamps[tickets, 8] int64 ns, points_per_chunk)``."""
-        if self._handle is None:
-            raise RuntimeError("chain_trace() needs a live handle: call generate once first")
-        lib = _lib.load()
-        cp = ctypes.c_int32()
-        if max_tickets is not None:
-            _lib.check(lib.bvx_chain_trace(self._handle, None, int(max_tickets), None, ctypes.byref(cp)),
-                       self._handle)
-            return None
-        n = ctypes.c_int32()
-        buf = np.zeros((1 << 16, 8), dtype=np.int64)
-        _lib.check(lib.bvx_chain_trace(self._handle, buf.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)),
-                                       buf.shape[0], ctypes.byref(n), ctypes.byref(cp)), self._handle)
-        return buf[:n.value].copy(), int(cp.value)
-
     # ---- VoxelGenerator.generate
     def generate(self, points, max_voxels=None):
         """(voxels, coordinates, num_points_per_voxel) of one frame."""

@@ -294,7 +294,7 @@ def run_ours(args):
     dom = max(per_kernel, key=per_kernel.get)
     ab = algorithmic_bytes(npts, F, m_voxels, T, C)
     # algorithmic bytes of each kernel = its share of the contract's compulsory I/O
-    k_bytes = {"k_chain": ab["points_in"],
+    k_bytes = {"k_insert": ab["points_in"],
                "k_gather": ab["voxels_out"] + ab["coors_out"] + ab["num_out"] + ab["mean_out"]}
     peak, peak_src = measured_peaks()
     dom_bytes = k_bytes.get(dom, 0)

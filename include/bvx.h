@@ -48,8 +48,8 @@ typedef enum bvx_status {
 #define BVX_OVERFLOW_BREAK 0
 #define BVX_OVERFLOW_CONTINUE 1
 
-/* Cell -> voxel lookup structure.  HASHED: open-addressing table sized by
- * max_voxels (L2 resident).  DENSE: one entry per grid cell, the layout
+/* Cell -> voxel lookup structure.  HASHED: open-addressing table sized by the
+ * number of points (L2 resident).  DENSE: one entry per grid cell, the layout
  * of the reference's cached `coor_to_voxelidx` grid. */
 #define BVX_GRID_HASHED 0
 #define BVX_GRID_DENSE 1
@@ -180,21 +180,12 @@ int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m,
 /* Optional per-kernel device timing: CUDA events are recorded on the call's
  * stream around every kernel of the pipeline while enabled.  bvx_profile_read
  * synchronises those events and returns accumulated milliseconds and launch
- * counts per kernel slot: 0 k_chain, 5 k_gather (other slots unused). */
+ * counts per kernel slot: 0 k_insert, 1 k_verify (+ rank scan), 3 k_slot,
+ * 4 k_overflow, 5 k_gather (slots 2, 6, 7 unused). */
 #define BVX_PROFILE_SLOTS 8
 int bvx_profile_enable(bvx_handle* h, int32_t on);
 int bvx_profile_read(bvx_handle* h, double ms[BVX_PROFILE_SLOTS],
                      int64_t launches[BVX_PROFILE_SLOTS], int32_t reset);
-
-/* Diagnostics of the chain kernel: with out == NULL, arm tracing for calls of up
- * to max_tickets chunk tickets (0 disarms).  With out != NULL, synchronise the
- * device and copy the last call's [tickets, 8] int64 nanosecond stamps
- * (ticket g = chunk_row * frames + frame; columns: 0 ticket taken, 1 chunk
- * prepared in shared memory, 2 previous chunk published, 3 table resolved,
- * 4 voxels numbered, 5 chain handed on, 6 bucket written, 7 unused; 0 = not
- * reached).  *chunk_points receives the points per chunk. */
-int bvx_chain_trace(bvx_handle* h, int64_t* out, int32_t max_tickets,
-                    int32_t* tickets, int32_t* chunk_points);
 
 /* Message of the last failing call on this handle (or, with h == NULL, of the
  * last failing handle-less call on this thread). */
