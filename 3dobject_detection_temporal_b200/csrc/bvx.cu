@@ -530,6 +530,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.ovf_cap = h->cfg.max_points;
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
     p.dbg = getenv("BVX_DEBUG_MODE") ? atoi(getenv("BVX_DEBUG_MODE")) : 0;
+    p.bulk_clear = (h->cfg.grid_kind == BVX_GRID_HASHED && !(p.dbg & 1)) ? 1 : 0;
     p.voxels = o.voxels;
     p.coors = o.coors;
     p.num_points = o.num_points;
@@ -538,6 +539,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
 
     const int T = p.T;
     const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
+    const int rchunks = p.bulk_clear ? 0 : chunks;      // per-entry reset blocks (dense grid only)
     if (chunks > 65535 || B > 65535)
         return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call and 67M points per frame");
     (void)max_words;
@@ -562,7 +564,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     if (small) {
         const int tiles = (cap + kBlock - 1) / kBlock;
         const size_t smem = (size_t)kWarps * 32 * T * 16;
-        const dim3 grid(tiles + chunks, B);
+        const dim3 grid(tiles + rchunks, B);
         ProfScope ps(h, 5, st);
         switch (T) {
 #define BVX_GS(TT) case TT: launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p, tiles); break;
@@ -578,7 +580,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         if (smem > 48 * 1024)
             CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ProfScope ps(h, 5, st);
-        launch_k(h, k_gather, dim3(tiles + chunks, B), kBlock, smem, st, p, tiles, vt);
+        launch_k(h, k_gather, dim3(tiles + rchunks, B), kBlock, smem, st, p, tiles, vt);
     }
     if (o.voxel_num) {
         CK(h, cudaMemcpyAsync(o.voxel_num, p.frame_voxel_offsets + B, 4, cudaMemcpyDeviceToDevice, st));

@@ -105,6 +105,7 @@ struct Pipe {
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
     int dbg;             // BVX_DEBUG_MODE experiments (0 = product behaviour)
+    int bulk_clear;      // hashed tables: cleared by streaming stores in the gather (no per-entry reset)
     // outputs
     float* voxels;
     int* coors;
@@ -595,6 +596,19 @@ __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, 
     }
 }
 
+// Hashed tables are small (the next power of two above the frame's point count, 8 bytes per
+// slot): every gather block clears its slice of the frame's table with streaming 16-byte
+// stores -- sequential DRAM traffic instead of one random read-modify-write per entry.
+__device__ __forceinline__ void clear_table_slice(const Pipe& p, const FrameDesc& fr, int tiles)
+{
+    const unsigned int n2 = (fr.tbl_mask + 1u) >> 1;            // uint4 = two slots
+    const unsigned int per = (n2 + tiles - 1) / tiles;
+    const unsigned int lo = blockIdx.x * per, hi = min(n2, lo + per);
+    uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
+    const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+    for (unsigned int j = lo + threadIdx.x; j < hi; j += kBlock) __stcs(t4 + j, e);
+}
+
 __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int cell)
 {
     const int gx = p.g.gs[0], gy = p.g.gs[1];
@@ -620,6 +634,7 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
+    if (p.bulk_clear) clear_table_slice(p, fr, tiles);
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * kBlock;
     if (v0 >= mf) return;
@@ -694,6 +709,7 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
+    if (p.bulk_clear) clear_table_slice(p, fr, tiles);
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * vt;
     if (v0 >= mf) return;
