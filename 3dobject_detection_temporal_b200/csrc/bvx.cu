@@ -63,6 +63,11 @@ struct bvx_handle {
     cudaEvent_t pin_ev[kRing];
     size_t pin_bytes = 0;
     int pin_next = 0;
+    // pipelined host form: copy streams, per-sub-batch events, pinned scratch for the counts
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    std::vector<cudaEvent_t> ev_h2d, ev_done;
+    int32_t* pin_offs = nullptr;
+    size_t pin_offs_count = 0;
     // host-form staging
     void* stage_in = nullptr;
     size_t stage_in_bytes = 0;
@@ -74,6 +79,7 @@ struct bvx_handle {
     int* dev_coors = nullptr;
     int* dev_num = nullptr;
     int* dev_offs = nullptr;
+    int* dev_offs_sub = nullptr;   // per-sub-batch offsets of the pipelined host form
     size_t dev_out_voxels = 0;  // voxel capacity of the dev_* outputs
     int dev_out_tf = 0;
     // optional per-kernel timing (bvx_profile_*): CUDA events around every launch
@@ -191,10 +197,15 @@ extern "C" int bvx_destroy(bvx_handle* h)
     cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
     cudaFree(h->d_offsets_scratch);
     cudaFree(h->dev_points); cudaFree(h->dev_voxels); cudaFree(h->dev_coors);
-    cudaFree(h->dev_num); cudaFree(h->dev_offs);
+    cudaFree(h->dev_num); cudaFree(h->dev_offs); cudaFree(h->dev_offs_sub);
     for (int i = 0; i < bvx_handle::kRing; ++i) {
         if (h->pin[i]) { cudaFreeHost(h->pin[i]); cudaEventDestroy(h->pin_ev[i]); }
     }
+    if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+    if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    for (cudaEvent_t e : h->ev_h2d) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+    if (h->pin_offs) cudaFreeHost(h->pin_offs);
     if (h->stage_in) cudaFreeHost(h->stage_in);
     if (h->stage_out) cudaFreeHost(h->stage_out);
     for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
@@ -448,6 +459,7 @@ struct Outputs {
     float* mean;
     int mean_c;
     int coor_cols;
+    int frame_base;
 };
 
 // Launch with the table region marked L2-persisting (per-launch access policy window).
@@ -527,6 +539,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.cap = cap;
     p.overflow_continue = h->cfg.overflow_mode == BVX_OVERFLOW_CONTINUE;
     p.coor_cols = o.coor_cols;
+    p.frame_base = o.frame_base;
     p.ovf_cap = h->cfg.max_points;
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
     p.dbg = getenv("BVX_DEBUG_MODE") ? atoi(getenv("BVX_DEBUG_MODE")) : 0;
@@ -606,7 +619,7 @@ extern "C" int bvx_generate(bvx_handle* h, const float* points, int32_t n, int32
     if (n < 0 || (n > 0 && !points)) return fail(h, BVX_ERR_BAD_ARGUMENT, "bad points/n");
     bvx_sweep s = plain_sweep(points, n);
     std::vector<FrameSpec> fr(1, FrameSpec{&s, 1, 0});
-    Outputs o{voxels, coors, num_points, nullptr, voxel_num, nullptr, 0, 3};
+    Outputs o{voxels, coors, num_points, nullptr, voxel_num, nullptr, 0, 3, 0};
     return run_pipeline(h, fr, f, f, max_voxels, o, (cudaStream_t)stream);
 }
 
@@ -617,7 +630,7 @@ extern "C" int bvx_generate_sweeps(bvx_handle* h, const bvx_sweep* sweeps, int32
     if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
     if (k < 1 || !sweeps) return fail(h, BVX_ERR_BAD_ARGUMENT, "need at least one sweep");
     std::vector<FrameSpec> fr(1, FrameSpec{sweeps, k, 1});
-    Outputs o{voxels, coors, num_points, nullptr, voxel_num, nullptr, 0, 3};
+    Outputs o{voxels, coors, num_points, nullptr, voxel_num, nullptr, 0, 3, 0};
     return run_pipeline(h, fr, f_in, f_in + 1, max_voxels, o, (cudaStream_t)stream);
 }
 
@@ -637,7 +650,7 @@ extern "C" int bvx_generate_batched(bvx_handle* h, const float* points, const in
         if (sw[i].n > 0 && !points) return fail(h, BVX_ERR_BAD_ARGUMENT, "null points");
         fr[i] = FrameSpec{&sw[i], 1, 0};
     }
-    Outputs o{voxels, coors4, num_points, frame_voxel_offsets, nullptr, mean, mean_c, 4};
+    Outputs o{voxels, coors4, num_points, frame_voxel_offsets, nullptr, mean, mean_c, 4, 0};
     return run_pipeline(h, fr, f, f, max_voxels, o, (cudaStream_t)stream);
 }
 
@@ -658,7 +671,7 @@ static int ensure_host_buffers(bvx_handle* h, size_t in_bytes, size_t voxels, in
         h->dev_points_bytes = in_bytes;
     }
     if (voxels > h->dev_out_voxels || tf > h->dev_out_tf) {
-        cudaFree(h->dev_voxels); cudaFree(h->dev_coors); cudaFree(h->dev_num); cudaFree(h->dev_offs);
+        cudaFree(h->dev_voxels); cudaFree(h->dev_coors); cudaFree(h->dev_num); cudaFree(h->dev_offs); cudaFree(h->dev_offs_sub);
         h->dev_voxels = nullptr; h->dev_coors = nullptr; h->dev_num = nullptr; h->dev_offs = nullptr;
         const size_t v = std::max(voxels, h->dev_out_voxels);
         const int t2 = std::max(tf, h->dev_out_tf);
@@ -666,6 +679,7 @@ static int ensure_host_buffers(bvx_handle* h, size_t in_bytes, size_t voxels, in
         CK(h, cudaMalloc((void**)&h->dev_coors, v * 16));
         CK(h, cudaMalloc((void**)&h->dev_num, v * 4));
         CK(h, cudaMalloc((void**)&h->dev_offs, ((size_t)h->cfg.max_frames + 1) * 4));
+        CK(h, cudaMalloc((void**)&h->dev_offs_sub, ((size_t)h->cfg.max_frames + 16) * 2 * 4));
         h->dev_out_voxels = v;
         h->dev_out_tf = t2;
     }
@@ -680,7 +694,12 @@ static int stage_in(bvx_handle* h, const void* src, size_t bytes, cudaStream_t s
         return BVX_OK;
     }
     if (bytes > h->stage_in_bytes) {
-        if (h->stage_in) cudaFreeHost(h->stage_in);
+        if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+    if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    for (cudaEvent_t e : h->ev_h2d) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+    if (h->pin_offs) cudaFreeHost(h->pin_offs);
+    if (h->stage_in) cudaFreeHost(h->stage_in);
         h->stage_in = nullptr;
         CK(h, cudaMallocHost(&h->stage_in, bytes));
         h->stage_in_bytes = bytes;
@@ -724,6 +743,92 @@ static int stage_out(bvx_handle* h, void* dst[3], const void* src[3], const size
     return BVX_OK;
 }
 
+// Pinned host buffers, B >= 2 frames: the batch is cut into sub-batches and the three legs
+// run on three streams -- H2D of sub-batch k+1, the kernels of sub-batch k and the D2H of
+// sub-batch k-1 overlap, so the call costs about max(H2D, D2H) on the full-duplex PCIe link
+// instead of H2D + kernels + D2H.  Results land in the caller's buffers exactly as in the
+// unpipelined form (concatenated in frame order, global batch index in the coordinates).
+static int generate_batched_pipelined(bvx_handle* h, const float* points, const int32_t* offs, int b, int f,
+                                      int cap, float* voxels, int32_t* coors4, int32_t* num_points,
+                                      int32_t* fvo_host, cudaStream_t st)
+{
+    const int T = h->cfg.max_num_points;
+    const int nsub = std::min(b, 8);
+    const int fs = (b + nsub - 1) / nsub;                 // frames per sub-batch
+    const int ns = (b + fs - 1) / fs;
+    if (!h->s_h2d) CK(h, cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+    if (!h->s_d2h) CK(h, cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+    while ((int)h->ev_h2d.size() < ns) {
+        cudaEvent_t e;
+        CK(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->ev_h2d.push_back(e);
+    }
+    while ((int)h->ev_done.size() < ns + 1) {
+        cudaEvent_t e;
+        CK(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->ev_done.push_back(e);
+    }
+    const size_t need = (size_t)ns * (fs + 1);
+    if (need > h->pin_offs_count) {
+        if (h->pin_offs) cudaFreeHost(h->pin_offs);
+        h->pin_offs = nullptr;
+        CK(h, cudaMallocHost((void**)&h->pin_offs, need * 4));
+        h->pin_offs_count = need;
+    }
+    // the copy streams start after whatever the caller queued on its stream
+    CK(h, cudaEventRecord(h->ev_done[ns], st));
+    CK(h, cudaStreamWaitEvent(h->s_h2d, h->ev_done[ns], 0));
+    // leg 1: every H2D copy, back to back on the copy-in stream
+    for (int k = 0; k < ns; ++k) {
+        const int f0 = k * fs, f1 = std::min(b, f0 + fs);
+        const size_t p0 = (size_t)offs[f0], p1 = (size_t)offs[f1];
+        if (p1 > p0)
+            CK(h, cudaMemcpyAsync(h->dev_points + p0 * f, points + p0 * f, (p1 - p0) * f * 4,
+                                  cudaMemcpyHostToDevice, h->s_h2d));
+        CK(h, cudaEventRecord(h->ev_h2d[k], h->s_h2d));
+    }
+    // leg 2: the kernels of each sub-batch on the caller's stream, outputs at capacity stride
+    std::vector<int32_t> loc(fs + 1);
+    for (int k = 0; k < ns; ++k) {
+        const int f0 = k * fs, f1 = std::min(b, f0 + fs), bk = f1 - f0;
+        for (int i = 0; i <= bk; ++i) loc[i] = offs[f0 + i] - offs[f0];
+        CK(h, cudaStreamWaitEvent(st, h->ev_h2d[k], 0));
+        std::vector<bvx_sweep> sw(bk);
+        std::vector<FrameSpec> fr(bk);
+        for (int i = 0; i < bk; ++i) {
+            sw[i] = plain_sweep(h->dev_points + (size_t)offs[f0 + i] * f, loc[i + 1] - loc[i]);
+            fr[i] = FrameSpec{&sw[i], 1, 0};
+        }
+        const size_t v0 = (size_t)f0 * cap;
+        Outputs o{h->dev_voxels + v0 * T * f, h->dev_coors + v0 * 4, h->dev_num + v0,
+                  h->dev_offs_sub + (size_t)k * (fs + 1), nullptr, nullptr, 0, 4, f0};
+        int rc = run_pipeline(h, fr, f, f, cap, o, st);
+        if (rc) return rc;
+        CK(h, cudaMemcpyAsync(h->pin_offs + (size_t)k * (fs + 1), h->dev_offs_sub + (size_t)k * (fs + 1),
+                              ((size_t)bk + 1) * 4, cudaMemcpyDeviceToHost, st));
+        CK(h, cudaEventRecord(h->ev_done[k], st));
+    }
+    // leg 3: as each sub-batch finishes, its M rows go home on the copy-out stream
+    size_t run = 0;
+    fvo_host[0] = 0;
+    for (int k = 0; k < ns; ++k) {
+        const int f0 = k * fs, f1 = std::min(b, f0 + fs), bk = f1 - f0;
+        CK(h, cudaEventSynchronize(h->ev_done[k]));
+        const int32_t* lo = h->pin_offs + (size_t)k * (fs + 1);
+        const size_t m = (size_t)lo[bk], v0 = (size_t)f0 * cap;
+        for (int i = 1; i <= bk; ++i) fvo_host[f0 + i] = (int32_t)(run + (size_t)lo[i]);
+        if (m > 0) {
+            CK(h, cudaMemcpyAsync(voxels + run * T * f, h->dev_voxels + v0 * T * f, m * T * f * 4,
+                                  cudaMemcpyDeviceToHost, h->s_d2h));
+            CK(h, cudaMemcpyAsync(coors4 + run * 4, h->dev_coors + v0 * 4, m * 16, cudaMemcpyDeviceToHost, h->s_d2h));
+            CK(h, cudaMemcpyAsync(num_points + run, h->dev_num + v0, m * 4, cudaMemcpyDeviceToHost, h->s_d2h));
+        }
+        run += m;
+    }
+    CK(h, cudaStreamSynchronize(h->s_d2h));
+    return BVX_OK;
+}
+
 extern "C" int bvx_generate_batched_host(bvx_handle* h, const float* points, const int32_t* offs, int32_t b,
                                          int32_t f, int32_t max_voxels, float* voxels, int32_t* coors4,
                                          int32_t* num_points, int32_t* fvo_host, void* stream)
@@ -737,6 +842,8 @@ extern "C" int bvx_generate_batched_host(bvx_handle* h, const float* points, con
     const size_t n = (size_t)offs[b];
     int rc = ensure_host_buffers(h, n * f * 4, (size_t)cap * b, T * f);
     if (rc) return rc;
+    if (b >= 2 && n > 0 && is_pinned(points) && is_pinned(voxels) && is_pinned(coors4) && is_pinned(num_points))
+        return generate_batched_pipelined(h, points, offs, b, f, cap, voxels, coors4, num_points, fvo_host, st);
     if ((rc = stage_in(h, points, n * f * 4, st))) return rc;
     rc = bvx_generate_batched(h, h->dev_points, offs, b, f, cap, h->dev_voxels, h->dev_coors, h->dev_num,
                               h->dev_offs, nullptr, 0, st);

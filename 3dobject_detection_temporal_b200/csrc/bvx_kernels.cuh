@@ -102,6 +102,7 @@ struct Pipe {
     int cap;             // per-frame max_voxels of this call
     int overflow_continue;
     int coor_cols;       // 3 (single frame) or 4 (batched, batch index first)
+    int frame_base;      // batch index of frame 0 of this call (sub-batches of a pipelined host call)
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
     int dbg;             // BVX_DEBUG_MODE experiments (0 = product behaviour)
@@ -615,7 +616,7 @@ __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int 
     const int x = cell % gx, r = cell / gx;
     const int y = r % gy, z = r / gy;
     if (p.coor_cols == 4) {
-        reinterpret_cast<int4*>(p.coors)[gv] = make_int4(f, z, y, x);
+        reinterpret_cast<int4*>(p.coors)[gv] = make_int4(f + p.frame_base, z, y, x);
     } else {
         int* c = p.coors + gv * 3;
         c[0] = z; c[1] = y; c[2] = x;

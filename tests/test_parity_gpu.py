@@ -188,6 +188,28 @@ def test_batched(pkg, oracle, synth, overflow):
     assert np.array_equal(sep.view(np.uint32), mean.view(np.uint32))
 
 
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_batched_host_pipelined(pkg, oracle, synth, overflow):
+    """Pinned host buffers take the pipelined path (sub-batches on three streams); results
+    must be identical to the plain host form, for ragged batches with empty frames too."""
+    for sizes in ([5000, 0, 33, 12001, 1, 7000, 0, 0, 2500, 900, 15000], [300, 200], [0, 0, 0],
+                  [4000] * 19):
+        frames = [synth.lidar_frame(n, "kitti", seed=70 + i) for i, n in enumerate(sizes)]
+        g, o = _pair(pkg, oracle, KITTI, 5, 1500, overflow)
+        wv, wc, wn, woff = o.generate_batched(frames)
+        cat = np.concatenate(frames, axis=0)
+        offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+        hp = pkg.pinned_empty(cat.shape, np.float32)
+        hp[:] = cat
+        b, cap = len(sizes), 1500
+        out = (pkg.pinned_empty((b * cap, 5, 4), np.float32), pkg.pinned_empty((b * cap, 4), np.int32),
+               pkg.pinned_empty((b * cap,), np.int32), pkg.pinned_empty((b + 1,), np.int32))
+        for _ in range(2):                      # second call: workspace and events reused
+            hv, hc, hn, hoff = g.generate_batched(hp, offs, out=out)
+            assert np.array_equal(hoff, woff), sizes
+            _eq((hv, hc, hn), (wv, wc, wn), f"pipelined host {sizes[:3]}")
+
+
 def test_handle_growth_and_reuse(pkg, oracle, synth):
     g, o = _pair(pkg, oracle, KITTI, 5, 2000)
     for n in (1000, 50000, 200, 80000, 50000):
