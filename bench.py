@@ -301,8 +301,15 @@ def run_ours(args):
     achieved = dom_bytes / (per_kernel[dom] * 1e-3) / 1e9
     pipe_bytes = sum(ab.values())
     pipe_gbs = pipe_bytes / (ms_step * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
+    # capture of this workload (profiles/r01_b_ncu_full_summary.txt); cold L2, cfg4 with 64 frames only
+    ncu_traffic = {"k_insert": 118.50e6 + 25.51e6, "k_verify": 80.40e6 + 3.99e6,
+                   "k_slot": 100.76e6 + 5.06e6, "k_gather": 74.94e6 + 185.18e6}
+    traffic = ncu_traffic.get(dom) if (B == 64 and args.overflow == "break") else None
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "profiles/r01_b_ncu_full_summary.txt (ncu --set full, cold L2)",
+                "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": dom_bytes,
                 "kernel_ms": per_kernel[dom], "kernel_share_of_step": per_kernel[dom] / ksum,
                 "per_kernel_ms": per_kernel,
