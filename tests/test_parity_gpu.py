@@ -62,6 +62,20 @@ def test_host_form_numpy_roundtrip(pkg, oracle, synth, overflow):
     _eq(g.generate(pp), o.generate(pts), "pinned host form")
 
 
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_many_more_cells_than_cap(pkg, oracle, synth, overflow):
+    """Far more distinct cells than max_voxels (the table is sized by the point count, not by
+    the cap); results must not change, and the next call must start from a clean workspace."""
+    pts = synth.lidar_frame(40000, "kitti", seed=21)
+    for cap in (64, 300, 5000):
+        g, o = _pair(pkg, oracle, KITTI, 5, cap, overflow)
+        want = o.generate(pts)
+        for _ in range(2):
+            _eq(g.generate(torch.from_numpy(pts).cuda()), want, f"cap={cap} {overflow}")
+        small = synth.lidar_frame(900, "kitti", seed=22)          # same handle, tiny frame afterwards
+        _eq(g.generate(torch.from_numpy(small).cuda()), o.generate(small), "after overflow")
+
+
 def test_unshuffled_ring_order(pkg, oracle, synth):
     pts = synth.lidar_frame(40000, "kitti", seed=5, shuffle=False)
     for overflow in ("break", "continue"):
