@@ -20,4 +20,9 @@ def __getattr__(name):
         import importlib
         mod = importlib.import_module(__name__ + ".modules")
         return mod if name == "modules" else getattr(mod, name)
+    if name in ("anchors_area", "anchors_mask", "sparse_sum_for_anchors_mask", "fused_get_anchors_area",
+                "anchors"):
+        import importlib
+        mod = importlib.import_module(__name__ + ".anchors")
+        return mod if name == "anchors" else getattr(mod, name)
     raise AttributeError(name)

@@ -71,6 +71,14 @@ SYMBOLS = {
     "bvx_host_free": (ctypes.c_int, [_vp]),
     "bvx_mean_vfe": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_scatter_bev": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "bvx_anchors_area_workspace_bytes": (ctypes.c_size_t, [_i32, _i32, _i32, _i32]),
+    "bvx_anchors_area": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(ctypes.c_float),
+                                        ctypes.POINTER(ctypes.c_float), ctypes.POINTER(_i32), _i32, _vp, _i32,
+                                        _vp, ctypes.c_size_t, _vp, _vp]),
+    "bvx_sparse_sum_for_anchors_mask": (ctypes.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "bvx_fused_get_anchors_area": (ctypes.c_int, [_vp, _i32, _i32, _vp, _i32, ctypes.POINTER(ctypes.c_float),
+                                                  ctypes.POINTER(ctypes.c_float), ctypes.POINTER(_i32), _vp,
+                                                  _vp]),
     "bvx_profile_enable": (ctypes.c_int, [_vp, _i32]),
     "bvx_profile_read": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64),
                                         _i32]),

@@ -17,6 +17,7 @@
 
 #include "bvx.h"
 #include "bvx_kernels.cuh"
+#include "bvx_anchors.cuh"
 
 using namespace bvx;
 
@@ -956,5 +957,126 @@ extern "C" int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "scatter launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+// ---------------------------------------------------------------- anchors area
+static bool aa_layout(int32_t batch, int32_t ny, int32_t nx, int32_t max_voxels_per_frame, AnchorsMap* mp)
+{
+    if (batch < 1 || ny < 1 || nx < 1 || max_voxels_per_frame < 0) return false;
+    mp->batch = batch; mp->ny = ny; mp->nx = nx;
+    mp->packed = (max_voxels_per_frame <= 65535 && (nx % 2) == 0) ? 1 : 0;
+    mp->wn = mp->packed ? nx / 2 : nx;
+    mp->words = nullptr;
+    return true;
+}
+
+extern "C" size_t bvx_anchors_area_workspace_bytes(int32_t batch, int32_t ny, int32_t nx,
+                                                   int32_t max_voxels_per_frame)
+{
+    AnchorsMap mp;
+    if (!aa_layout(batch, ny, nx, max_voxels_per_frame, &mp)) return 0;
+    return (((size_t)batch * ny * mp.wn * 4) + 15) & ~(size_t)15;
+}
+
+extern "C" int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_cols, int32_t batch,
+                                const float voxel_size_xy[2], const float range_xy0[2],
+                                const int32_t grid_xy[2], int32_t max_voxels_per_frame,
+                                const float* anchors_bv, int32_t n_anchors, void* workspace,
+                                size_t workspace_bytes, float* area, void* stream)
+{
+    if (!voxel_size_xy || !range_xy0 || !grid_xy) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    AnchorsMap mp;
+    if (m < 0 || n_anchors < 0 || (coor_cols != 3 && coor_cols != 4) ||
+        !aa_layout(batch, grid_xy[1], grid_xy[0], max_voxels_per_frame, &mp))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad anchors-area shape");
+    if (coor_cols == 3 && batch != 1)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "[M,3] coordinates carry no batch index: batch must be 1");
+    if (!(voxel_size_xy[0] > 0.f) || !(voxel_size_xy[1] > 0.f))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "voxel size must be positive");
+    if (n_anchors == 0) return BVX_OK;
+    if (!workspace || !area || !anchors_bv || (m > 0 && !coors))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    const size_t need = bvx_anchors_area_workspace_bytes(batch, mp.ny, mp.nx, max_voxels_per_frame);
+    if (workspace_bytes < need) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "workspace too small: need %zu bytes", need);
+    if (((uintptr_t)workspace & 15) || ((uintptr_t)anchors_bv & 15) || (coor_cols == 4 && ((uintptr_t)coors & 15)))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "workspace/anchors/coors must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    mp.words = static_cast<unsigned int*>(workspace);
+    const size_t n4 = need >> 4;
+    const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
+    k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(workspace), n4, nullptr, 0);
+    g_launches += 1;
+    if (m > 0) {
+        k_aa_hist<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, mp);
+        const long long rows = (long long)batch * mp.ny;
+        const unsigned rb = (unsigned)((rows + 7) / 8);
+        if ((mp.wn & 3) == 0) k_aa_rowscan<4><<<rb, 256, 0, st>>>(mp);
+        else k_aa_rowscan<1><<<rb, 256, 0, st>>>(mp);
+        const size_t smem = (size_t)mp.ny * kAaStripWords * sizeof(unsigned int);
+        if (smem <= 200 * 1024) {
+            static std::atomic<size_t> smem_set{0};
+            if (smem > 48 * 1024 && smem_set.load() < smem) {
+                cudaFuncSetAttribute(k_aa_colscan, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+                smem_set.store(200 * 1024);
+            }
+            k_aa_colscan<<<dim3((mp.wn + kAaStripWords - 1) / kAaStripWords, batch), kAaColThreads, smem, st>>>(mp);
+        } else {
+            k_aa_colscan_serial<<<dim3((mp.wn + 255) / 256, batch), 256, 0, st>>>(mp);
+        }
+        g_launches += 3;
+    }
+    AnchorsQuery q;
+    q.stride[0] = voxel_size_xy[0]; q.stride[1] = voxel_size_xy[1];
+    q.offset[0] = range_xy0[0]; q.offset[1] = range_xy0[1];
+    q.gx = mp.nx; q.gy = mp.ny;
+    k_aa_query<<<dim3((n_anchors + 255) / 256, batch), 256, 0, st>>>(mp, anchors_bv, n_anchors, q, area);
+    g_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "anchors-area launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+extern "C" int bvx_sparse_sum_for_anchors_mask(const int32_t* coors, int32_t m, int32_t coor_cols, int32_t ny,
+                                               int32_t nx, float* ret, void* stream)
+{
+    if (m < 0 || ny < 1 || nx < 1 || (coor_cols != 3 && coor_cols != 4))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad sparse-sum shape");
+    if (!ret || (m > 0 && !coors)) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    if ((uintptr_t)ret & 15) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "ret must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t total = (size_t)ny * nx, n4 = total >> 2;
+    const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
+    k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(ret), n4, ret + (n4 << 2), (int)(total & 3));
+    g_launches += 1;
+    if (m > 0) {
+        k_aa_hist_f32<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, coor_cols - 2, ny, nx, ret);
+        g_launches += 1;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "sparse-sum launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+extern "C" int bvx_fused_get_anchors_area(const float* dense_map, int32_t ny, int32_t nx, const float* anchors_bv,
+                                          int32_t n_anchors, const float stride_xy[2], const float offset_xy[2],
+                                          const int32_t grid_xy[2], float* ret, void* stream)
+{
+    if (ny < 1 || nx < 1 || n_anchors < 0 || !stride_xy || !offset_xy || !grid_xy || grid_xy[0] < 1 || grid_xy[1] < 1)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad anchors-area shape");
+    if (!(stride_xy[0] > 0.f) || !(stride_xy[1] > 0.f))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "stride must be positive");
+    if (n_anchors == 0) return BVX_OK;
+    if (!dense_map || !anchors_bv || !ret) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    if ((uintptr_t)anchors_bv & 15) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "anchors must be 16-byte aligned");
+    AnchorsQuery q;
+    q.stride[0] = stride_xy[0]; q.stride[1] = stride_xy[1];
+    q.offset[0] = offset_xy[0]; q.offset[1] = offset_xy[1];
+    q.gx = grid_xy[0]; q.gy = grid_xy[1];
+    k_aa_query_f32<<<(n_anchors + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dense_map, ny, nx, anchors_bv,
+                                                                                n_anchors, q, ret);
+    g_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "anchors-area launch: %s", cudaGetErrorString(e));
     return BVX_OK;
 }

@@ -177,6 +177,47 @@ int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m,
                     int32_t c, int32_t b, int32_t d, int32_t ny, int32_t nx,
                     float* canvas, void* stream);
 
+/* Anchors area from voxel coordinates, the computation
+ * behind the reference's anchors_mask:
+ *   dense = sparse_sum_for_anchors_mask(coors, (ny, nx))      second/core/box_np_ops.py:776-781
+ *   dense = dense.cumsum(0).cumsum(1)                         second/kittiviewer/viewer.py:397-398
+ *   area  = fused_get_anchors_area(dense, anchors_bv,         second/core/box_np_ops.py:784-810
+ *                                  voxel_size, range, grid)
+ * in one call, for every frame of a batch, without leaving the device.
+ * coors: [m, coor_cols] int32, rows (z, y, x) (coor_cols 3, batch must be 1) or
+ * (b, z, y, x) (coor_cols 4) -- exactly what bvx_generate / bvx_generate_batched
+ * wrote.  grid_xy = grid_size x, y (the map is [grid_xy[1], grid_xy[0]]).
+ * anchors_bv: [n_anchors, 4] float32 rows (x0, y0, x1, y1), shared by the frames.
+ * area: [batch, n_anchors] float32 voxel counts; the caller thresholds it
+ * (anchor_area_threshold, second/protos/input_reader.proto:23).
+ * max_voxels_per_frame bounds the rows any one frame contributes (selects 16- or
+ * 32-bit table cells).  workspace: device scratch of at least
+ * bvx_anchors_area_workspace_bytes(...) bytes, 16-byte aligned.
+ * Anchors wholly outside the range index out of bounds in the reference; here
+ * their corners are clamped into the map. */
+size_t bvx_anchors_area_workspace_bytes(int32_t batch, int32_t ny, int32_t nx,
+                                        int32_t max_voxels_per_frame);
+int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_cols,
+                     int32_t batch, const float voxel_size_xy[2],
+                     const float range_xy0[2], const int32_t grid_xy[2],
+                     int32_t max_voxels_per_frame, const float* anchors_bv,
+                     int32_t n_anchors, void* workspace, size_t workspace_bytes,
+                     float* area, void* stream);
+
+/* The same two reference functions under their own names, for callers that keep
+ * the reference's decomposition (float32 maps, the caller does the two cumsums).
+ * ret: [ny, nx] float32, zero filled by the call; the y, x columns of coors are
+ * the last two (box_np_ops.py:779 reads columns 1, 2 of [M, 3]). */
+int bvx_sparse_sum_for_anchors_mask(const int32_t* coors, int32_t m,
+                                    int32_t coor_cols, int32_t ny, int32_t nx,
+                                    float* ret, void* stream);
+int bvx_fused_get_anchors_area(const float* dense_map, int32_t ny, int32_t nx,
+                               const float* anchors_bv, int32_t n_anchors,
+                               const float stride_xy[2],
+                               const float offset_xy[2],
+                               const int32_t grid_xy[2], float* ret,
+                               void* stream);
+
 /* Optional per-kernel device timing: CUDA events are recorded on the call's
  * stream around every kernel of the pipeline while enabled.  bvx_profile_read
  * synchronises those events and returns accumulated milliseconds and launch

@@ -153,3 +153,45 @@ def test_batched_oracle_contract(oracle, synth):
     assert off[1] == off[2]                                  # empty frame
     for b in range(3):
         assert (c[off[b]:off[b + 1], 0] == b).all()           # batch index first (voxelnet.py:285)
+
+
+ANCHOR_TAGS = ("pillar", "second", "odd_nx")
+
+
+def test_anchors_area_matches_reference_golden(oracle, golden_dir):
+    """The restated sparse_sum_for_anchors_mask / fused_get_anchors_area against outputs of the
+    reference's own functions (tests/golden/make_golden_anchors.py)."""
+    z = np.load(os.path.join(golden_dir, "anchors_reference.npz"))
+    for tag in ANCHOR_TAGS:
+        grid, coors = z[f"{tag}_grid"], z[f"{tag}_coors"]
+        hist = oracle.sparse_sum_for_anchors_mask(coors, (int(grid[1]), int(grid[0])))
+        want = np.zeros_like(hist)
+        nz = z[f"{tag}_hist_nonzero"]
+        want[nz[:, 0], nz[:, 1]] = z[f"{tag}_hist_values"]
+        assert np.array_equal(hist, want)
+        area = oracle.anchors_area(coors, z[f"{tag}_anchors_bv"], z[f"{tag}_voxel_size"], z[f"{tag}_range"], grid)
+        assert area.dtype == np.float32 and np.array_equal(area, z[f"{tag}_area"])
+        # [M, 4] rows (b, z, y, x) read the same two columns
+        c4 = np.concatenate([np.zeros((coors.shape[0], 1), np.int32), coors], 1)
+        assert np.array_equal(oracle.anchors_area(c4, z[f"{tag}_anchors_bv"], z[f"{tag}_voxel_size"],
+                                                  z[f"{tag}_range"], grid), z[f"{tag}_area"])
+
+
+def test_anchors_area_is_a_box_count(oracle):
+    """Size-independent property: the area is the number of voxels whose (y, x) lies in the
+    half-open cell rectangle (c0, c2] x (c1, c3] -- the summed-area-table identity."""
+    rng = np.random.default_rng(3)
+    vs = np.asarray([0.25, 0.5, 1.0], np.float32)
+    rg = np.asarray([-8, -6, -1, 8, 6, 1], np.float32)
+    grid = oracle.grid_size(vs, rg)
+    coors = np.stack([rng.integers(0, grid[2], 900), rng.integers(0, grid[1], 900),
+                      rng.integers(0, grid[0], 900)], 1).astype(np.int32)
+    lo = np.stack([rng.uniform(-8, 7, 300), rng.uniform(-6, 5, 300)], 1)
+    bv = np.concatenate([lo, lo + rng.uniform(0.1, 4, (300, 2))], 1).astype(np.float32)
+    got = oracle.anchors_area(coors, bv, vs, rg, grid)
+    c = np.floor((bv - rg[[0, 1, 0, 1]]) / vs[[0, 1, 0, 1]]).astype(np.int64)
+    c[:, 0] = np.maximum(c[:, 0], 0); c[:, 1] = np.maximum(c[:, 1], 0)
+    c[:, 2] = np.minimum(c[:, 2], grid[0] - 1); c[:, 3] = np.minimum(c[:, 3], grid[1] - 1)
+    y, x = coors[:, 1][None], coors[:, 2][None]
+    want = ((x > c[:, 0:1]) & (x <= c[:, 2:3]) & (y > c[:, 1:2]) & (y <= c[:, 3:4])).sum(1)
+    assert np.array_equal(got, want.astype(np.float32))
