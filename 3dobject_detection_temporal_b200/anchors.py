@@ -82,9 +82,9 @@ def anchors_area(coors, anchors_bv, voxel_size, point_cloud_range, grid_size, ba
     grid = _i2(grid_size)
     cap = int(m if max_voxels_per_frame is None else max_voxels_per_frame)
     lib = _lib.load()
-    need = lib.bvx_anchors_area_workspace_bytes(b, grid[1], grid[0], cap)
+    need = lib.bvx_anchors_area_workspace_bytes(b, grid[1], grid[0], cap, m)
     if need == 0:
-        raise ValueError("bad anchors-area shape")
+        raise ValueError("bad or unsupported anchors-area shape")
     key = q.device.index
     ws = _WS.get(key)
     if ws is None or ws.numel() < need:

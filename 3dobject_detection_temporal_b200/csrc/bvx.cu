@@ -961,22 +961,45 @@ extern "C" int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_
 }
 
 // ---------------------------------------------------------------- anchors area
-static bool aa_layout(int32_t batch, int32_t ny, int32_t nx, int32_t max_voxels_per_frame, AnchorsMap* mp)
+struct AaLayout {
+    AnchorsMap mp;
+    size_t off_above, off_cnt, off_off, off_fill, off_binned, bytes;   // byte offsets into the workspace
+    size_t smem;
+};
+
+static size_t aa_round16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+static bool aa_layout(int32_t batch, int32_t ny, int32_t nx, int32_t max_voxels_per_frame, int32_t m, AaLayout* L)
 {
-    if (batch < 1 || ny < 1 || nx < 1 || max_voxels_per_frame < 0) return false;
-    mp->batch = batch; mp->ny = ny; mp->nx = nx;
-    mp->packed = (max_voxels_per_frame <= 65535 && (nx % 2) == 0) ? 1 : 0;
-    mp->wn = mp->packed ? nx / 2 : nx;
-    mp->words = nullptr;
+    if (batch < 1 || ny < 1 || nx < 1 || max_voxels_per_frame < 0 || m < 0 || nx >= (1 << kAaYShift)) return false;
+    AnchorsMap& mp = L->mp;
+    mp.batch = batch; mp.ny = ny; mp.nx = nx;
+    mp.packed = (max_voxels_per_frame <= 65535 && (nx % 2) == 0) ? 1 : 0;
+    mp.wn = mp.packed ? nx / 2 : nx;
+    // band height: as many rows as fit 48 KB of shared memory (4 blocks per SM), at most 32
+    int h = kAaMaxBandRows, hs = 5;
+    while (h > 1 && (size_t)h * mp.wn * 4 > 48 * 1024) { h >>= 1; --hs; }
+    L->smem = (size_t)h * mp.wn * 4;
+    if (L->smem > 200 * 1024) return false;            // one row must fit in shared memory
+    mp.h = h; mp.hshift = hs; mp.nb = (ny + h - 1) / h;
+    if ((long long)batch * mp.nb > (1 << 28)) return false;
+    const size_t keys = (size_t)batch * mp.nb;
+    size_t o = aa_round16((size_t)batch * ny * mp.wn * 4);
+    L->off_above = o;  o += aa_round16(keys * mp.wn * 4);
+    L->off_cnt = o;    o += aa_round16(keys * 4);
+    L->off_fill = o;   o += aa_round16(keys * 4);
+    L->off_off = o;    o += aa_round16((keys + 1) * 4);
+    L->off_binned = o; o += aa_round16((size_t)m * 4);
+    L->bytes = o;
     return true;
 }
 
 extern "C" size_t bvx_anchors_area_workspace_bytes(int32_t batch, int32_t ny, int32_t nx,
-                                                   int32_t max_voxels_per_frame)
+                                                   int32_t max_voxels_per_frame, int32_t m)
 {
-    AnchorsMap mp;
-    if (!aa_layout(batch, ny, nx, max_voxels_per_frame, &mp)) return 0;
-    return (((size_t)batch * ny * mp.wn * 4) + 15) & ~(size_t)15;
+    AaLayout L;
+    if (!aa_layout(batch, ny, nx, max_voxels_per_frame, m, &L)) return 0;
+    return L.bytes;
 }
 
 extern "C" int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_cols, int32_t batch,
@@ -986,10 +1009,10 @@ extern "C" int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_co
                                 size_t workspace_bytes, float* area, void* stream)
 {
     if (!voxel_size_xy || !range_xy0 || !grid_xy) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
-    AnchorsMap mp;
-    if (m < 0 || n_anchors < 0 || (coor_cols != 3 && coor_cols != 4) ||
-        !aa_layout(batch, grid_xy[1], grid_xy[0], max_voxels_per_frame, &mp))
-        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad anchors-area shape");
+    AaLayout L;
+    if (n_anchors < 0 || (coor_cols != 3 && coor_cols != 4) ||
+        !aa_layout(batch, grid_xy[1], grid_xy[0], max_voxels_per_frame, m, &L))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad or unsupported anchors-area shape");
     if (coor_cols == 3 && batch != 1)
         return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "[M,3] coordinates carry no batch index: batch must be 1");
     if (!(voxel_size_xy[0] > 0.f) || !(voxel_size_xy[1] > 0.f))
@@ -997,41 +1020,49 @@ extern "C" int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_co
     if (n_anchors == 0) return BVX_OK;
     if (!workspace || !area || !anchors_bv || (m > 0 && !coors))
         return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
-    const size_t need = bvx_anchors_area_workspace_bytes(batch, mp.ny, mp.nx, max_voxels_per_frame);
-    if (workspace_bytes < need) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "workspace too small: need %zu bytes", need);
+    if (workspace_bytes < L.bytes)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "workspace too small: need %zu bytes", L.bytes);
     if (((uintptr_t)workspace & 15) || ((uintptr_t)anchors_bv & 15) || (coor_cols == 4 && ((uintptr_t)coors & 15)))
         return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "workspace/anchors/coors must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    mp.words = static_cast<unsigned int*>(workspace);
-    const size_t n4 = need >> 4;
-    const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
-    k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(workspace), n4, nullptr, 0);
+    AnchorsMap& mp = L.mp;
+    char* ws = static_cast<char*>(workspace);
+    mp.words = reinterpret_cast<unsigned int*>(ws);
+    mp.above = reinterpret_cast<unsigned int*>(ws + L.off_above);
+    mp.cnt = reinterpret_cast<int*>(ws + L.off_cnt);
+    mp.fill = reinterpret_cast<int*>(ws + L.off_fill);
+    mp.off = reinterpret_cast<int*>(ws + L.off_off);
+    mp.binned = reinterpret_cast<unsigned int*>(ws + L.off_binned);
+    // counting sort of the voxels by (frame, band); cnt and fill are adjacent
+    const size_t n4 = (L.off_off - L.off_cnt) >> 4;
+    const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock, 148 * 8);
+    k_fill_zero<<<std::max(fb, 1), kBlock, 0, st>>>(reinterpret_cast<float4*>(ws + L.off_cnt), n4, nullptr, 0);
     g_launches += 1;
     if (m > 0) {
-        k_aa_hist<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, mp);
-        const long long rows = (long long)batch * mp.ny;
-        const unsigned rb = (unsigned)((rows + 7) / 8);
-        if ((mp.wn & 3) == 0) k_aa_rowscan<4><<<rb, 256, 0, st>>>(mp);
-        else k_aa_rowscan<1><<<rb, 256, 0, st>>>(mp);
-        const size_t smem = (size_t)mp.ny * kAaStripWords * sizeof(unsigned int);
-        if (smem <= 200 * 1024) {
-            static std::atomic<size_t> smem_set{0};
-            if (smem > 48 * 1024 && smem_set.load() < smem) {
-                cudaFuncSetAttribute(k_aa_colscan, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-                smem_set.store(200 * 1024);
-            }
-            k_aa_colscan<<<dim3((mp.wn + kAaStripWords - 1) / kAaStripWords, batch), kAaColThreads, smem, st>>>(mp);
-        } else {
-            k_aa_colscan_serial<<<dim3((mp.wn + 255) / 256, batch), 256, 0, st>>>(mp);
-        }
-        g_launches += 3;
+        k_aa_count<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, mp);
+        g_launches += 1;
     }
+    k_aa_offsets<<<1, 1024, 0, st>>>(mp);
+    g_launches += 1;
+    if (m > 0) {
+        k_aa_bin<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, mp);
+        g_launches += 1;
+    }
+    static std::atomic<int> smem_set{0};
+    if (L.smem > 48 * 1024 && !smem_set.load()) {
+        cudaFuncSetAttribute(k_aa_band<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(k_aa_band<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        smem_set.store(1);
+    }
+    if ((mp.wn & 3) == 0) k_aa_band<4><<<dim3(mp.nb, batch), 256, L.smem, st>>>(mp);
+    else k_aa_band<1><<<dim3(mp.nb, batch), 256, L.smem, st>>>(mp);
+    k_aa_above<<<dim3((mp.wn + 255) / 256, batch), 256, 0, st>>>(mp);
     AnchorsQuery q;
     q.stride[0] = voxel_size_xy[0]; q.stride[1] = voxel_size_xy[1];
     q.offset[0] = range_xy0[0]; q.offset[1] = range_xy0[1];
     q.gx = mp.nx; q.gy = mp.ny;
     k_aa_query<<<dim3((n_anchors + 255) / 256, batch), 256, 0, st>>>(mp, anchors_bv, n_anchors, q, area);
-    g_launches += 1;
+    g_launches += 3;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "anchors-area launch: %s", cudaGetErrorString(e));
     return BVX_OK;

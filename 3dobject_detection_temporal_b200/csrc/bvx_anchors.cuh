@@ -14,43 +14,63 @@
 // a cell-wise add for both (a packed half never carries: no table entry exceeds the
 // frame's voxel count).
 //
-//   k_aa_hist     one thread per voxel: atomicAdd into the zeroed word map
-//   k_aa_rowscan  one warp per row: inclusive prefix along x, 4 words per lane
-//   k_aa_colscan  one block per (16-word column strip, frame): the whole strip sits
-//                 in shared memory, 32 row segments scanned in parallel, one DRAM
-//                 read + one DRAM write per word
-//   k_aa_query    one thread per (anchor, frame): four corner reads
+// The histogram is sparse (<= max_voxels cells of a map of millions), so the dense
+// map is never zero-filled, read back or scanned in global memory.  The map is cut
+// into bands of H rows; the voxels are binned by (frame, band) with a counting sort,
+// and each band is built, scanned both ways and written exactly once from shared
+// memory.  The table is BANDED -- T(y, x) = band-local table + prefix of the bands
+// above, kept as a second, small table -- so no pass depends on another band:
+//   S(y, x) = band_table[y][x] + above[y / H][x]
+//
+//   k_aa_count / k_aa_offsets / k_aa_bin   counting sort of the voxels by (frame, band)
+//   k_aa_band     one block per (band, frame): histogram in shared memory, prefix
+//                 along x, prefix along y, one coalesced write of the band
+//   k_aa_above    exclusive prefix of the band totals over the bands of a frame
+//   k_aa_query    one thread per (anchor, frame): four corners, two reads each
+// DRAM traffic: one write of the table (2 bytes per map cell) + the corner reads.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace bvx {
 
-constexpr int kAaStripWords = 16;   // column strip width of k_aa_colscan (64 bytes per row)
-constexpr int kAaColThreads = 512;  // 16 lanes x 32 row segments
-constexpr int kAaSegs = kAaColThreads / kAaStripWords;
+constexpr int kAaMaxBandRows = 32;
+constexpr int kAaYShift = 27;            // binned voxel = (row inside the band << 27) | x
 
 struct AnchorsMap {
-    unsigned int* words;  // [batch][ny][wn]
+    unsigned int* words;   // banded table [batch][ny][wn]
+    unsigned int* above;   // [batch][nb][wn]: totals of the bands above (band totals before k_aa_above)
+    int* cnt;              // [batch * nb] voxels per (frame, band)
+    int* off;              // [batch * nb + 1] exclusive prefix of cnt
+    int* fill;             // [batch * nb] bin cursors
+    unsigned int* binned;  // [m] voxels grouped by (frame, band)
     int batch, ny, nx;
-    int wn;               // words per row: nx / 2 (packed) or nx
-    int packed;           // 1: two 16-bit cells per word
+    int wn;                // words per row: nx / 2 (packed) or nx
+    int packed;            // 1: two 16-bit cells per word
+    int h;                 // band height (power of two), hshift = log2(h)
+    int hshift;
+    int nb;                // bands per frame
 };
+
+__device__ __forceinline__ unsigned int aa_word_cell(unsigned int w, int x, int packed)
+{
+    return packed ? (w >> ((x & 1) * 16)) & 0xFFFFu : w;
+}
 
 __device__ __forceinline__ unsigned int aa_cell(const AnchorsMap& mp, int b, int y, int x)
 {
-    const size_t row = ((size_t)b * mp.ny + y) * mp.wn;
-    if (mp.packed) return (__ldg(mp.words + row + (x >> 1)) >> ((x & 1) * 16)) & 0xFFFFu;
-    return __ldg(mp.words + row + x);
+    const int wx = mp.packed ? x >> 1 : x;
+    const unsigned int t = __ldg(mp.words + ((size_t)b * mp.ny + y) * mp.wn + wx);
+    const unsigned int a = __ldg(mp.above + ((size_t)b * mp.nb + (y >> mp.hshift)) * mp.wn + wx);
+    return aa_word_cell(t, x, mp.packed) + aa_word_cell(a, x, mp.packed);
 }
 
 // coors rows are (z, y, x) [cols == 3, single frame] or (b, z, y, x) [cols == 4].
-__global__ void __launch_bounds__(256) k_aa_hist(const int* __restrict__ coors, int m, int cols,
-                                                 const AnchorsMap mp)
+// Rows outside the map or the batch are ignored (like the BEV scatter).
+__device__ __forceinline__ bool aa_voxel(const int* __restrict__ coors, int i, int cols, const AnchorsMap& mp,
+                                         int& b, int& y, int& x)
 {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    if (i >= m) return;
-    int b = 0, y, x;
+    b = 0;
     if (cols == 4) {
         const int4 q = __ldg(reinterpret_cast<const int4*>(coors) + i);
         b = q.x; y = q.z; x = q.w;
@@ -58,11 +78,56 @@ __global__ void __launch_bounds__(256) k_aa_hist(const int* __restrict__ coors, 
         y = __ldg(coors + 3 * (size_t)i + 1);
         x = __ldg(coors + 3 * (size_t)i + 2);
     }
-    if ((unsigned)b >= (unsigned)mp.batch || (unsigned)y >= (unsigned)mp.ny || (unsigned)x >= (unsigned)mp.nx)
-        return;
-    const size_t row = ((size_t)b * mp.ny + y) * mp.wn;
-    if (mp.packed) atomicAdd(mp.words + row + (x >> 1), 1u << ((x & 1) * 16));
-    else atomicAdd(mp.words + row + x, 1u);
+    return (unsigned)b < (unsigned)mp.batch && (unsigned)y < (unsigned)mp.ny && (unsigned)x < (unsigned)mp.nx;
+}
+
+__global__ void __launch_bounds__(256) k_aa_count(const int* __restrict__ coors, int m, int cols,
+                                                  const AnchorsMap mp)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    int b, y, x;
+    if (i < m && aa_voxel(coors, i, cols, mp, b, y, x)) atomicAdd(mp.cnt + b * mp.nb + (y >> mp.hshift), 1);
+}
+
+// one block: off = exclusive prefix of cnt over the batch * nb bins
+__global__ void __launch_bounds__(1024) k_aa_offsets(const AnchorsMap mp)
+{
+    __shared__ int s_w[32];
+    __shared__ int s_carry;
+    const int n = mp.batch * mp.nb;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += 1024) {
+        const int i = i0 + threadIdx.x;
+        const int v = i < n ? mp.cnt[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (lane == 31) s_w[wid] = inc;
+        __syncthreads();
+        int base = s_carry;
+        for (int k = 0; k < wid; ++k) base += s_w[k];
+        if (i < n) mp.off[i] = base + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = base + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) mp.off[n] = s_carry;
+}
+
+__global__ void __launch_bounds__(256) k_aa_bin(const int* __restrict__ coors, int m, int cols,
+                                                const AnchorsMap mp)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    int b, y, x;
+    if (i >= m || !aa_voxel(coors, i, cols, mp, b, y, x)) return;
+    const int key = b * mp.nb + (y >> mp.hshift);
+    const int pos = mp.off[key] + atomicAdd(mp.fill + key, 1);
+    mp.binned[pos] = ((unsigned)(y & (mp.h - 1)) << kAaYShift) | (unsigned)x;
 }
 
 // inclusive prefix of one word given the running sum of everything to its left
@@ -82,91 +147,92 @@ __device__ __forceinline__ unsigned int aa_word_total(unsigned int w, int packed
     return packed ? (w & 0xFFFFu) + (w >> 16) : w;
 }
 
-// One warp per row.  V = 4: rows are 16-byte aligned and wn % 4 == 0 (uint4 accesses).
+// grid (nb, batch), 256 threads, dynamic smem = h * wn words.
+// V = 4: wn % 4 == 0 (16-byte row stores).
 template <int V>
-__global__ void __launch_bounds__(256) k_aa_rowscan(const AnchorsMap mp)
+__global__ void __launch_bounds__(256) k_aa_band(const AnchorsMap mp)
 {
+    extern __shared__ __align__(16) unsigned int aa_s[];
+    const int band = blockIdx.x, f = blockIdx.y;
+    const int y0 = band << mp.hshift;
+    const int rows = min(mp.h, mp.ny - y0);
+    const int wn = mp.wn;
+    const int key = f * mp.nb + band;
+    const int j0 = mp.off[key], j1 = mp.off[key + 1];
+    unsigned int* g = mp.words + ((size_t)f * mp.ny + y0) * wn;
+    unsigned int* tot = mp.above + (size_t)key * wn;
+    if (j0 == j1) {                      // empty band: zeros
+        for (int w = threadIdx.x * V; w < wn; w += 256 * V) {
+            for (int r = 0; r < rows; ++r) {
+                if (V == 4) *reinterpret_cast<uint4*>(g + (size_t)r * wn + w) = make_uint4(0u, 0u, 0u, 0u);
+                else g[(size_t)r * wn + w] = 0u;
+            }
+            if (V == 4) *reinterpret_cast<uint4*>(tot + w) = make_uint4(0u, 0u, 0u, 0u);
+            else tot[w] = 0u;
+        }
+        return;
+    }
+    for (int k = threadIdx.x; k < rows * wn; k += 256) aa_s[k] = 0u;
+    __syncthreads();
+    for (int j = j0 + threadIdx.x; j < j1; j += 256) {
+        const unsigned int e = __ldg(mp.binned + j);
+        const int yl = e >> kAaYShift, x = e & ((1u << kAaYShift) - 1u);
+        if (mp.packed) atomicAdd(aa_s + yl * wn + (x >> 1), 1u << ((x & 1) * 16));
+        else atomicAdd(aa_s + yl * wn + x, 1u);
+    }
+    __syncthreads();
+    // prefix along x: one warp per row, 32 words per step
     const int lane = threadIdx.x & 31;
-    const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (row >= (long long)mp.batch * mp.ny) return;
-    unsigned int* r = mp.words + (size_t)row * mp.wn;
-    unsigned int carry = 0;
-    for (int w0 = 0; w0 < mp.wn; w0 += 32 * V) {
-        const int w = w0 + lane * V;
-        unsigned int v[V];
-        if (V == 4) {
-            uint4 q = make_uint4(0u, 0u, 0u, 0u);
-            if (w < mp.wn) q = *reinterpret_cast<const uint4*>(r + w);
-            v[0] = q.x; v[1 % V] = q.y; v[2 % V] = q.z; v[3 % V] = q.w;
-        } else {
+    for (int r = threadIdx.x >> 5; r < rows; r += 8) {
+        unsigned int* row = aa_s + r * wn;
+        unsigned int carry = 0;
+        for (int w0 = 0; w0 < wn; w0 += 32) {
+            const int w = w0 + lane;
+            const unsigned int v = w < wn ? row[w] : 0u;
+            const unsigned int t = aa_word_total(v, mp.packed);
+            unsigned int inc = t;
 #pragma unroll
-            for (int k = 0; k < V; ++k) v[k] = (w + k < mp.wn) ? r[w + k] : 0u;
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned int u = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += u;
+            }
+            unsigned int run = carry + inc - t;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+            if (w < wn) row[w] = aa_word_prefix(v, run, mp.packed);
         }
-        unsigned int tot = 0;
+    }
+    __syncthreads();
+    // prefix along y inside the band, written straight to the table (coalesced rows)
+    for (int w = threadIdx.x * V; w < wn; w += 256 * V) {
+        unsigned int acc[V];
 #pragma unroll
-        for (int k = 0; k < V; ++k) tot += aa_word_total(v[k], mp.packed);
-        unsigned int inc = tot;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned int t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += t;
+        for (int k = 0; k < V; ++k) acc[k] = 0u;
+        for (int r = 0; r < rows; ++r) {
+            if (V == 4) {
+                const uint4 q = *reinterpret_cast<const uint4*>(aa_s + r * wn + w);
+                acc[0] += q.x; acc[1 % V] += q.y; acc[2 % V] += q.z; acc[3 % V] += q.w;
+                *reinterpret_cast<uint4*>(g + (size_t)r * wn + w) = make_uint4(acc[0], acc[1 % V], acc[2 % V], acc[3 % V]);
+            } else {
+                acc[0] += aa_s[r * wn + w];
+                g[(size_t)r * wn + w] = acc[0];
+            }
         }
-        unsigned int run = carry + inc - tot;
-        carry += __shfl_sync(0xffffffffu, inc, 31);
-#pragma unroll
-        for (int k = 0; k < V; ++k) v[k] = aa_word_prefix(v[k], run, mp.packed);
-        if (V == 4) {
-            if (w < mp.wn) *reinterpret_cast<uint4*>(r + w) = make_uint4(v[0], v[1 % V], v[2 % V], v[3 % V]);
-        } else {
-#pragma unroll
-            for (int k = 0; k < V; ++k)
-                if (w + k < mp.wn) r[w + k] = v[k];
-        }
+        if (V == 4) *reinterpret_cast<uint4*>(tot + w) = make_uint4(acc[0], acc[1 % V], acc[2 % V], acc[3 % V]);
+        else tot[w] = acc[0];
     }
 }
 
-// grid (strips, batch), 512 threads, dynamic smem = ny * 16 words.  Thread t owns
-// column t % 16 of row segment t / 16.
-__global__ void __launch_bounds__(kAaColThreads) k_aa_colscan(const AnchorsMap mp)
+// above[f][band][w] <- sum of the totals of bands 0 .. band-1 (in place)
+__global__ void __launch_bounds__(256) k_aa_above(const AnchorsMap mp)
 {
-    extern __shared__ unsigned int aa_s[];
-    __shared__ unsigned int s_tot[kAaSegs][kAaStripWords], s_off[kAaSegs][kAaStripWords];
-    const int c0 = blockIdx.x * kAaStripWords;
-    const int col = threadIdx.x % kAaStripWords, seg = threadIdx.x / kAaStripWords;
-    const bool live = c0 + col < mp.wn;
-    unsigned int* g = mp.words + (size_t)blockIdx.y * mp.ny * mp.wn + c0 + col;
-    // load: thread (col, seg) reads rows seg, seg + 32, ... (two rows per warp instruction)
-    for (int y = seg; y < mp.ny; y += kAaSegs)
-        aa_s[y * kAaStripWords + col] = live ? __ldcs(g + (size_t)y * mp.wn) : 0u;
-    __syncthreads();
-    const int per = (mp.ny + kAaSegs - 1) / kAaSegs;
-    const int y0 = seg * per, y1 = min(mp.ny, y0 + per);
-    unsigned int acc = 0;
-    for (int y = y0; y < y1; ++y) {
-        acc += aa_s[y * kAaStripWords + col];
-        aa_s[y * kAaStripWords + col] = acc;
-    }
-    s_tot[seg][col] = acc;
-    __syncthreads();
-    unsigned int above = 0;
-    for (int s = 0; s < seg; ++s) above += s_tot[s][col];
-    s_off[seg][col] = above;
-    __syncthreads();
-    // store: row y gets the total of the segments above its own
-    for (int y = seg; y < mp.ny; y += kAaSegs)
-        if (live) g[(size_t)y * mp.wn] = aa_s[y * kAaStripWords + col] + s_off[y / per][col];
-}
-
-// Any ny (strip does not fit in shared memory): one thread per word column.
-__global__ void __launch_bounds__(256) k_aa_colscan_serial(const AnchorsMap mp)
-{
-    const int c = blockIdx.x * 256 + threadIdx.x;
-    if (c >= mp.wn) return;
-    unsigned int* g = mp.words + (size_t)blockIdx.y * mp.ny * mp.wn + c;
-    unsigned int acc = 0;
-    for (int y = 0; y < mp.ny; ++y) {
-        acc += g[(size_t)y * mp.wn];
-        g[(size_t)y * mp.wn] = acc;
+    const int w = blockIdx.x * 256 + threadIdx.x;
+    if (w >= mp.wn) return;
+    unsigned int* a = mp.above + (size_t)blockIdx.y * mp.nb * mp.wn + w;
+    unsigned int run = 0;
+    for (int b = 0; b < mp.nb; ++b) {
+        const unsigned int t = a[(size_t)b * mp.wn];
+        a[(size_t)b * mp.wn] = run;
+        run += t;
     }
 }
 

@@ -191,12 +191,15 @@ int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m,
  * area: [batch, n_anchors] float32 voxel counts; the caller thresholds it
  * (anchor_area_threshold, second/protos/input_reader.proto:23).
  * max_voxels_per_frame bounds the rows any one frame contributes (selects 16- or
- * 32-bit table cells).  workspace: device scratch of at least
- * bvx_anchors_area_workspace_bytes(...) bytes, 16-byte aligned.
+ * 32-bit table cells; a frame with more rows than this is undefined behaviour).
+ * workspace: device scratch of at least bvx_anchors_area_workspace_bytes(...,
+ * m) bytes, 16-byte aligned, contents irrelevant (0 is returned for shapes the
+ * library cannot serve: empty, or one map row larger than 200 KB).
  * Anchors wholly outside the range index out of bounds in the reference; here
  * their corners are clamped into the map. */
 size_t bvx_anchors_area_workspace_bytes(int32_t batch, int32_t ny, int32_t nx,
-                                        int32_t max_voxels_per_frame);
+                                        int32_t max_voxels_per_frame,
+                                        int32_t m);
 int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_cols,
                      int32_t batch, const float voxel_size_xy[2],
                      const float range_xy0[2], const int32_t grid_xy[2],
