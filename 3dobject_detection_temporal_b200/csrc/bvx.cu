@@ -963,7 +963,7 @@ extern "C" int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_
 // ---------------------------------------------------------------- anchors area
 struct AaLayout {
     AnchorsMap mp;
-    size_t off_above, off_cnt, off_off, off_fill, off_binned, bytes;   // byte offsets into the workspace
+    size_t off_above, off_cnt, off_fill, off_ticket, off_off, off_fbase, off_binned, bytes;   // byte offsets into the workspace
     size_t smem;
 };
 
@@ -986,9 +986,11 @@ static bool aa_layout(int32_t batch, int32_t ny, int32_t nx, int32_t max_voxels_
     const size_t keys = (size_t)batch * mp.nb;
     size_t o = aa_round16((size_t)batch * ny * mp.wn * 4);
     L->off_above = o;  o += aa_round16(keys * mp.wn * 4);
-    L->off_cnt = o;    o += aa_round16(keys * 4);
+    L->off_cnt = o;    o += aa_round16(keys * 4);      // cnt, fill, ticket: zeroed together every call
     L->off_fill = o;   o += aa_round16(keys * 4);
-    L->off_off = o;    o += aa_round16((keys + 1) * 4);
+    L->off_ticket = o; o += 16;
+    L->off_off = o;    o += aa_round16(keys * 4);
+    L->off_fbase = o;  o += aa_round16(((size_t)batch + 1) * 4);
     L->off_binned = o; o += aa_round16((size_t)m * 4);
     L->bytes = o;
     return true;
@@ -1031,21 +1033,23 @@ extern "C" int bvx_anchors_area(const int32_t* coors, int32_t m, int32_t coor_co
     mp.above = reinterpret_cast<unsigned int*>(ws + L.off_above);
     mp.cnt = reinterpret_cast<int*>(ws + L.off_cnt);
     mp.fill = reinterpret_cast<int*>(ws + L.off_fill);
+    mp.ticket = reinterpret_cast<int*>(ws + L.off_ticket);
     mp.off = reinterpret_cast<int*>(ws + L.off_off);
+    mp.frame_base = reinterpret_cast<int*>(ws + L.off_fbase);
     mp.binned = reinterpret_cast<unsigned int*>(ws + L.off_binned);
-    // counting sort of the voxels by (frame, band); cnt and fill are adjacent
+    // counting sort of the voxels by (frame, band)
     const size_t n4 = (L.off_off - L.off_cnt) >> 4;
     const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock, 148 * 8);
     k_fill_zero<<<std::max(fb, 1), kBlock, 0, st>>>(reinterpret_cast<float4*>(ws + L.off_cnt), n4, nullptr, 0);
     g_launches += 1;
     if (m > 0) {
-        k_aa_count<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, mp);
+        k_aa_count<<<(m + 1023) / 1024, 256, 0, st>>>(coors, m, coor_cols, mp);
         g_launches += 1;
     }
-    k_aa_offsets<<<1, 1024, 0, st>>>(mp);
+    k_aa_offsets<<<batch, 256, 0, st>>>(mp);
     g_launches += 1;
     if (m > 0) {
-        k_aa_bin<<<(m + 255) / 256, 256, 0, st>>>(coors, m, coor_cols, mp);
+        k_aa_bin<<<(m + 1023) / 1024, 256, 0, st>>>(coors, m, coor_cols, mp);
         g_launches += 1;
     }
     static std::atomic<int> smem_set{0};

@@ -41,8 +41,10 @@ struct AnchorsMap {
     unsigned int* words;   // banded table [batch][ny][wn]
     unsigned int* above;   // [batch][nb][wn]: totals of the bands above (band totals before k_aa_above)
     int* cnt;              // [batch * nb] voxels per (frame, band)
-    int* off;              // [batch * nb + 1] exclusive prefix of cnt
     int* fill;             // [batch * nb] bin cursors
+    int* ticket;           // [1] blocks of k_aa_offsets finished (zeroed with cnt and fill)
+    int* off;              // [batch * nb] exclusive prefix of cnt inside the frame
+    int* frame_base;       // [batch + 1] exclusive prefix of the frames' voxel counts
     unsigned int* binned;  // [m] voxels grouped by (frame, band)
     int batch, ny, nx;
     int wn;                // words per row: nx / 2 (packed) or nx
@@ -81,53 +83,118 @@ __device__ __forceinline__ bool aa_voxel(const int* __restrict__ coors, int i, i
     return (unsigned)b < (unsigned)mp.batch && (unsigned)y < (unsigned)mp.ny && (unsigned)x < (unsigned)mp.nx;
 }
 
+// Counting sort, both passes: a block takes 1024 consecutive voxels (almost always of one
+// frame) and bins them in shared memory first, so the global counters see one atomic per
+// (block, non-empty band) instead of one per voxel.  Voxels of another frame than the block's
+// first one (a block straddling a frame boundary), or maps with more than 1024 bands, go to
+// the global counters directly.
+constexpr int kAaSortPts = 4;
+constexpr int kAaSmemBins = 1024;
+
 __global__ void __launch_bounds__(256) k_aa_count(const int* __restrict__ coors, int m, int cols,
                                                   const AnchorsMap mp)
 {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    int b, y, x;
-    if (i < m && aa_voxel(coors, i, cols, mp, b, y, x)) atomicAdd(mp.cnt + b * mp.nb + (y >> mp.hshift), 1);
-}
-
-// one block: off = exclusive prefix of cnt over the batch * nb bins
-__global__ void __launch_bounds__(1024) k_aa_offsets(const AnchorsMap mp)
-{
-    __shared__ int s_w[32];
-    __shared__ int s_carry;
-    const int n = mp.batch * mp.nb;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    for (int i0 = 0; i0 < n; i0 += 1024) {
-        const int i = i0 + threadIdx.x;
-        const int v = i < n ? mp.cnt[i] : 0;
-        int inc = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += t;
-        }
-        if (lane == 31) s_w[wid] = inc;
-        __syncthreads();
-        int base = s_carry;
-        for (int k = 0; k < wid; ++k) base += s_w[k];
-        if (i < n) mp.off[i] = base + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) s_carry = base + inc;
+    __shared__ int s_bin[kAaSmemBins];
+    const int i0 = blockIdx.x * (256 * kAaSortPts);
+    const bool staged = mp.nb <= kAaSmemBins;
+    const int f0 = cols == 4 ? __ldg(coors + 4 * (size_t)i0) : 0;
+    if (staged) {
+        for (int k = threadIdx.x; k < mp.nb; k += 256) s_bin[k] = 0;
         __syncthreads();
     }
-    if (threadIdx.x == 0) mp.off[n] = s_carry;
+#pragma unroll
+    for (int k = 0; k < kAaSortPts; ++k) {
+        const int i = i0 + k * 256 + threadIdx.x;
+        int b, y, x;
+        if (i >= m || !aa_voxel(coors, i, cols, mp, b, y, x)) continue;
+        const int band = y >> mp.hshift;
+        if (staged && b == f0) atomicAdd(s_bin + band, 1);
+        else atomicAdd(mp.cnt + b * mp.nb + band, 1);
+    }
+    if (!staged || (unsigned)f0 >= (unsigned)mp.batch) return;
+    __syncthreads();
+    for (int k = threadIdx.x; k < mp.nb; k += 256)
+        if (s_bin[k]) atomicAdd(mp.cnt + f0 * mp.nb + k, s_bin[k]);
+}
+
+// grid (batch), 256 threads: off = exclusive prefix of cnt inside each frame; the last block
+// to finish turns the frame totals into frame_base.
+__global__ void __launch_bounds__(256) k_aa_offsets(const AnchorsMap mp)
+{
+    __shared__ int sm[kWarps + 1];
+    __shared__ int s_last;
+    const int f = blockIdx.x;
+    int carry = 0;
+    for (int k0 = 0; k0 < mp.nb; k0 += 256) {
+        const int k = k0 + threadIdx.x;
+        const int v = k < mp.nb ? mp.cnt[f * mp.nb + k] : 0;
+        int tot;
+        const int ex = block_exclusive_scan(v, &tot, sm);
+        if (k < mp.nb) mp.off[f * mp.nb + k] = carry + ex;
+        carry += tot;
+    }
+    if (threadIdx.x == 0) {
+        mp.frame_base[f + 1] = carry;          // frame total for now
+        __threadfence();
+        s_last = (atomicAdd(mp.ticket, 1) == mp.batch - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    carry = 0;
+    for (int f0 = 0; f0 < mp.batch; f0 += 256) {
+        const int ff = f0 + threadIdx.x;
+        const int v = ff < mp.batch ? __ldcg(mp.frame_base + ff + 1) : 0;
+        int tot;
+        const int ex = block_exclusive_scan(v, &tot, sm);
+        __syncthreads();
+        if (ff < mp.batch) mp.frame_base[ff + 1] = carry + ex + v;
+        carry += tot;
+    }
+    if (threadIdx.x == 0) mp.frame_base[0] = 0;
 }
 
 __global__ void __launch_bounds__(256) k_aa_bin(const int* __restrict__ coors, int m, int cols,
                                                 const AnchorsMap mp)
 {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    int b, y, x;
-    if (i >= m || !aa_voxel(coors, i, cols, mp, b, y, x)) return;
-    const int key = b * mp.nb + (y >> mp.hshift);
-    const int pos = mp.off[key] + atomicAdd(mp.fill + key, 1);
-    mp.binned[pos] = ((unsigned)(y & (mp.h - 1)) << kAaYShift) | (unsigned)x;
+    __shared__ int s_bin[kAaSmemBins];
+    const int i0 = blockIdx.x * (256 * kAaSortPts);
+    const bool staged = mp.nb <= kAaSmemBins;
+    const int f0 = cols == 4 ? __ldg(coors + 4 * (size_t)i0) : 0;
+    if (staged) {
+        for (int k = threadIdx.x; k < mp.nb; k += 256) s_bin[k] = 0;
+        __syncthreads();
+    }
+    int key[kAaSortPts], rank[kAaSortPts];
+    unsigned int val[kAaSortPts];
+#pragma unroll
+    for (int k = 0; k < kAaSortPts; ++k) {
+        const int i = i0 + k * 256 + threadIdx.x;
+        int b, y, x;
+        key[k] = -1;
+        rank[k] = -1;                                   // -1: global path
+        if (i >= m || !aa_voxel(coors, i, cols, mp, b, y, x)) continue;
+        const int band = y >> mp.hshift;
+        key[k] = b * mp.nb + band;
+        val[k] = ((unsigned)(y & (mp.h - 1)) << kAaYShift) | (unsigned)x;
+        if (staged && b == f0) rank[k] = atomicAdd(s_bin + band, 1);
+    }
+    if (staged) {
+        __syncthreads();
+        if ((unsigned)f0 < (unsigned)mp.batch)
+            for (int k = threadIdx.x; k < mp.nb; k += 256) {
+                const int c = s_bin[k];
+                if (c) s_bin[k] = atomicAdd(mp.fill + f0 * mp.nb + k, c);   // the block's base in the bin
+            }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < kAaSortPts; ++k) {
+        if (key[k] < 0) continue;
+        const int f = key[k] / mp.nb;
+        const int in_bin = rank[k] >= 0 ? s_bin[key[k] - f * mp.nb] + rank[k] : atomicAdd(mp.fill + key[k], 1);
+        mp.binned[mp.frame_base[f] + mp.off[key[k]] + in_bin] = val[k];
+    }
 }
 
 // inclusive prefix of one word given the running sum of everything to its left
@@ -158,7 +225,7 @@ __global__ void __launch_bounds__(256) k_aa_band(const AnchorsMap mp)
     const int rows = min(mp.h, mp.ny - y0);
     const int wn = mp.wn;
     const int key = f * mp.nb + band;
-    const int j0 = mp.off[key], j1 = mp.off[key + 1];
+    const int j0 = mp.frame_base[f] + mp.off[key], j1 = j0 + mp.cnt[key];
     unsigned int* g = mp.words + ((size_t)f * mp.ny + y0) * wn;
     unsigned int* tot = mp.above + (size_t)key * wn;
     if (j0 == j1) {                      // empty band: zeros
@@ -172,7 +239,7 @@ __global__ void __launch_bounds__(256) k_aa_band(const AnchorsMap mp)
         }
         return;
     }
-    for (int k = threadIdx.x; k < rows * wn; k += 256) aa_s[k] = 0u;
+    for (int k = threadIdx.x; k < rows * wn; k += 256) aa_s[k] = 0u;   // (wn odd: rows are not 16-byte aligned)
     __syncthreads();
     for (int j = j0 + threadIdx.x; j < j1; j += 256) {
         const unsigned int e = __ldg(mp.binned + j);
@@ -181,25 +248,23 @@ __global__ void __launch_bounds__(256) k_aa_band(const AnchorsMap mp)
         else atomicAdd(aa_s + yl * wn + x, 1u);
     }
     __syncthreads();
-    // prefix along x: one warp per row, 32 words per step
+    // prefix along x: one warp per row, each lane a contiguous run of words (odd length: no
+    // bank conflicts), one warp scan of the lane totals per row
     const int lane = threadIdx.x & 31;
+    const int run_len = ((wn + 31) / 32) | 1;
     for (int r = threadIdx.x >> 5; r < rows; r += 8) {
         unsigned int* row = aa_s + r * wn;
-        unsigned int carry = 0;
-        for (int w0 = 0; w0 < wn; w0 += 32) {
-            const int w = w0 + lane;
-            const unsigned int v = w < wn ? row[w] : 0u;
-            const unsigned int t = aa_word_total(v, mp.packed);
-            unsigned int inc = t;
+        const int w0 = min(wn, lane * run_len), w1 = min(wn, w0 + run_len);
+        unsigned int t = 0;
+        for (int w = w0; w < w1; ++w) t += aa_word_total(row[w], mp.packed);
+        unsigned int inc = t;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const unsigned int u = __shfl_up_sync(0xffffffffu, inc, d);
-                if (lane >= d) inc += u;
-            }
-            unsigned int run = carry + inc - t;
-            carry += __shfl_sync(0xffffffffu, inc, 31);
-            if (w < wn) row[w] = aa_word_prefix(v, run, mp.packed);
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned int u = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += u;
         }
+        unsigned int run = inc - t;
+        for (int w = w0; w < w1; ++w) row[w] = aa_word_prefix(row[w], run, mp.packed);
     }
     __syncthreads();
     // prefix along y inside the band, written straight to the table (coalesced rows)
@@ -222,17 +287,23 @@ __global__ void __launch_bounds__(256) k_aa_band(const AnchorsMap mp)
     }
 }
 
-// above[f][band][w] <- sum of the totals of bands 0 .. band-1 (in place)
+// above[f][band][w] <- sum of the totals of bands 0 .. band-1 (in place), 16 bands' loads in
+// flight per thread.
 __global__ void __launch_bounds__(256) k_aa_above(const AnchorsMap mp)
 {
     const int w = blockIdx.x * 256 + threadIdx.x;
     if (w >= mp.wn) return;
     unsigned int* a = mp.above + (size_t)blockIdx.y * mp.nb * mp.wn + w;
     unsigned int run = 0;
-    for (int b = 0; b < mp.nb; ++b) {
-        const unsigned int t = a[(size_t)b * mp.wn];
-        a[(size_t)b * mp.wn] = run;
-        run += t;
+    for (int b0 = 0; b0 < mp.nb; b0 += 16) {
+        unsigned int v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = b0 + k < mp.nb ? __ldcg(a + (size_t)(b0 + k) * mp.wn) : 0u;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (b0 + k < mp.nb) a[(size_t)(b0 + k) * mp.wn] = run;
+            run += v[k];
+        }
     }
 }
 

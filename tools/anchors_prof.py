@@ -30,7 +30,7 @@ for _ in range(steps):
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / steps
 m = int(coors4.shape[0])
-map_bytes = B * 1600 * 1408 * 2
-print(f"frames={B} voxels={m} anchors={bv.shape[0]} call={ms*1e3:.1f}us  "
-      f"map={map_bytes/1e6:.0f}MB  5 map passes -> {5*map_bytes/ms/1e6:.0f} GB/s effective  "
-      f"mask true {int((out > 1).sum())}/{out.numel()}")
+table = B * 1600 * 1408 * 2                       # one write of the 16-bit banded table
+alg = table + m * 16 * 2 + out.numel() * 4 + bv.nbytes  # + coors read by both sort passes + areas out + anchors
+print(f"frames={B} voxels={m} anchors={bv.shape[0]} call={ms*1e3:.1f}us  algorithmic {alg/1e6:.0f} MB -> "
+      f"{alg/ms/1e6:.0f} GB/s  mask true {int((out > 1).sum())}/{out.numel()}")
