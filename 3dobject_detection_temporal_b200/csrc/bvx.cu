@@ -559,7 +559,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     (void)max_words;
     if (chunks > 0) {
         ProfScope ps(h, 0, st);
-        launch_k(h, k_insert, dim3(B, chunks), kBlock, 0, st, p);
+        const int G = getenv("BVX_INSERT_GROUP") ? std::max(1, std::min(B, atoi(getenv("BVX_INSERT_GROUP")))) : B;
+        launch_k(h, k_insert, dim3(G, chunks, (B + G - 1) / G), kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);

@@ -73,8 +73,8 @@ struct FrameState {
     int m;            // voxels kept = min(total, cap)
     int istar;        // break cut-off: points with index >= istar are dropped
     int done_verify;  // chunks of k_verify finished (last-block detection); reset by the scanner
-    int next_chunk;   // k_insert: next chunk of the frame to hand out (in index order)
-    int distinct;     // k_insert: cells claimed so far by finished chunks
+    unsigned long long ticket;  // k_insert: low 32 bits = next chunk of the frame to hand out (in index
+                                // order), high 32 bits = cells claimed so far -- one atomic returns both
     int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
     int n_done;       // points that went through k_insert (prefix), published by the scan
 };
@@ -212,30 +212,32 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // 32-point mask word per k.
 //
 // Break early exit (the reference's serial loop stops at the point that would open
-// voxel #cap): before taking its ticket a block reads the number of distinct cells
-// claimed by finished chunks.  If that already exceeds cap, every point that was
-// inserted lies in a chunk with a smaller ticket, so the cut-off index i* lies
-// before this chunk and the chunk is skipped (nothing it holds can be kept).
-// Skipping is monotone, so the inserted points always form a prefix [0, n_eff).
+// voxel #cap): the ticket counter carries, in its high half, the number of distinct
+// cells claimed so far (every warp adds its new cells when it is done).  A block
+// gets its ticket and that count from ONE atomic.  If the count already exceeds cap,
+// every cell it counts was claimed by a chunk with a smaller ticket, so the cut-off
+// index i* lies before this chunk and the chunk is skipped (nothing it holds can be
+// kept).  The count only grows, so skipping is monotone in the ticket and the
+// inserted points always form a prefix [0, n_eff).
 //
 // Table protocol, CAS first, in ROUNDS (one atomic per point in flight, 4 per
-// thread -- the kernel is bound by L2 atomic round trips, tools/microbench2.cu):
+// thread):
 //   atomicCAS(empty -> {cell, i}):  was empty   -> new cell, I am a candidate
 //                                   same cell   -> atomicMin if my index is smaller
 //                                   other cell  -> probe the next slot
-__global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
+__global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
 {
     __shared__ int s_chunk;
-    __shared__ int s_new[kWarps];
-    const int f = blockIdx.x;
+    const int f = blockIdx.z * gridDim.x + blockIdx.x;
+    if (f >= p.nframes) return;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.y * kChunk >= fr.n) return;
     FrameState* st = p.state + f;
+    const bool brk = !p.overflow_continue;
     if (threadIdx.x == 0) {
-        const int d = __ldcg(&st->distinct);           // read BEFORE the ticket (see above)
-        __threadfence();                               // ... and ordered before it
-        int c = atomicAdd(&st->next_chunk, 1);
-        if (!p.overflow_continue && d > p.cap && c * kChunk < fr.n) {
+        const unsigned long long t = atomicAdd(&st->ticket, 1ull);
+        int c = (int)(unsigned int)t;
+        if (brk && (int)(t >> 32) > p.cap && c * kChunk < fr.n) {
             atomicMin(&st->n_eff, c * kChunk);
             c = 0x7FFFFFF;                             // skipped
         }
@@ -258,7 +260,8 @@ __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
             cell[k] = cell_of(p.g, x, y, z);
         }
     }
-    unsigned int active = 0, needmin = 0, wonmask = 0, newmask = 0;
+    unsigned int active = 0, needmin = 0, wonmask = 0;
+    int nnew = 0;
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
         h[k] = 0;
@@ -267,7 +270,7 @@ __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
             active |= 1u << k;
         }
     }
-    while (active) {
+    while (__any_sync(0xffffffffu, active)) {          // warp-uniform rounds
         unsigned long long r[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
                 if ((unsigned)r[k] > i) wonmask |= bit;
                 active &= ~bit;
             } else if (r[k] == kEmpty64) {
-                wonmask |= bit; newmask |= bit; active &= ~bit;
+                wonmask |= bit; ++nnew; active &= ~bit;
             } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
                 if ((unsigned)r[k] > i) needmin |= bit; else active &= ~bit;
             } else {
@@ -295,26 +298,18 @@ __global__ void __launch_bounds__(kBlock) k_insert(const Pipe p)
             }
         }
     }
-    int nnew = 0;
+    if (brk) {
+        // publish the cells this warp claimed; later tickets see them in their ticket word
+        nnew = __reduce_add_sync(0xffffffffu, nnew);
+        if (nnew && (threadIdx.x & 31) == 0) atomicAdd(&st->ticket, (unsigned long long)nnew << 32);
+    }
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
         const int i = base + k * kBlock + threadIdx.x;
         if (i < fr.n) p.slot[fr.pt_off + i] = cell[k] >= 0 ? (int)h[k] : -1;
         const unsigned int b = __ballot_sync(0xffffffffu, (wonmask >> k) & 1u);
-        nnew += __popc(__ballot_sync(0xffffffffu, (newmask >> k) & 1u));
         const int w = i >> 5;
         if ((threadIdx.x & 31) == 0 && w < fr.nwords) p.cand[fr.word_off + w] = b;
-    }
-    if (!p.overflow_continue) {
-        // publish the cells this chunk claimed; later tickets read it before they start
-        if ((threadIdx.x & 31) == 0) s_new[threadIdx.x >> 5] = nnew;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            int t = 0;
-#pragma unroll
-            for (int w = 0; w < kWarps; ++w) t += s_new[w];
-            if (t) atomicAdd(&st->distinct, t);
-        }
     }
 }
 
@@ -485,8 +480,7 @@ __global__ void __launch_bounds__(kBlock) k_slot(const Pipe p)
     const FrameDesc fr = p.frames[f];
     const int lim = min(p.state[f].n_done, p.state[f].istar);
     if (blockIdx.x == 0 && threadIdx.x == 0) {   // k_insert's per-frame counters, for the next call
-        p.state[f].next_chunk = 0;
-        p.state[f].distinct = 0;
+        p.state[f].ticket = 0ull;
         p.state[f].n_eff = 0x7FFFFFFF;
     }
     const unsigned long long* tbl = p.table + fr.tbl_off;

@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--overflow", default="break", choices=["break", "continue"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not pin the process to the GPU's NUMA node")
     ap.add_argument("--extra", action="store_true", help="also time cfg1/2/3/5 single calls")
     return ap.parse_args()
 
@@ -231,6 +232,7 @@ def run_ours(args):
         raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = None if args.no_numa_bind else pkg.shard.bind_host_to_device(local)   # before any pinned allocation
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -341,7 +343,8 @@ def run_ours(args):
         mo = int(r[3][-1])
         e2e = {"value": total_pts / dt / 1e6, "unit": UNIT, "ms_per_step": dt * 1e3, "steps": ksteps,
                "h2d_bytes_per_step": int(host.nbytes), "d2h_bytes_per_step": int(mo * (T * F * 4 + 16 + 4) + 4 * (B + 1)),
-               "api": "VoxelGenerator.generate_batched(numpy) -> bvx_generate_batched_host; pinned host buffers"}
+               "api": "VoxelGenerator.generate_batched(numpy) -> bvx_generate_batched_host; pinned host buffers",
+               "host_numa_binding": numa}
         gen_h.close()
     clocks = sampler.stop() if rank == 0 else None
 
