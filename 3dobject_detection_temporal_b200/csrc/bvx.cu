@@ -567,7 +567,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         launch_k(h, k_verify, dim3(std::max(chunks, 1), B), kBlock, 0, st, p);
     }
     if (chunks > 0) {
-        { ProfScope ps(h, 3, st); launch_k(h, k_slot, dim3(std::min(chunks, 32), B), kBlock, 0, st, p); }
+        { ProfScope ps(h, 3, st); launch_k(h, k_slot, dim3(std::min(chunks, std::max(32, (148 * 8 + B - 1) / B)), B), kBlock, 0, st, p); }
         if (T > kChainMaxT) {
             const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
             ProfScope ps(h, 4, st);
@@ -587,9 +587,14 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
 #undef BVX_GS
         }
     } else {
-        const int vt = std::max(1, kBlock / T);
+        // voxels per tile: ~256 bucket entries, ~1024 for long buckets (few of their entries are live)
+        int vt = std::max(1, (T > 32 ? 1024 : kBlock) / T);
+        auto tile_smem = [&](int v) {
+            return (size_t)(((v * T + 3) & ~3) + ((v + 3) & ~3)) * 4 + (size_t)v * T * f_out * 4;
+        };
+        while (vt > 1 && tile_smem(vt) > 48 * 1024) vt >>= 1;
         const int tiles = (cap + vt - 1) / vt;
-        const size_t smem = (size_t)((vt * T + 3) & ~3) * 4 + (size_t)vt * T * f_out * 4;
+        const size_t smem = tile_smem(vt);
         if (smem > 200 * 1024)
             return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", smem);
         if (smem > 48 * 1024)

@@ -697,7 +697,7 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
 // General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T bucket
 // entries) staged through shared memory; entries are rank-sorted in shared memory
 // (the large-T bucket is unordered).
-// grid (tiles + reset chunks, B); dynamic smem: round4(E) ints + E*f_out floats, E = vt*T.
+// grid (tiles + reset chunks, B); dynamic smem: round4(E) + round4(vt) ints + E*f_out floats, E = vt*T.
 __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int vt)
 {
     extern __shared__ int smem_i[];
@@ -712,27 +712,40 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
     const int nv = min(vt, mf - v0);
     const int E = nv * T;
     int* sidx = smem_i;
-    float* srow = reinterpret_cast<float*>(smem_i + ((vt * T + 3) & ~3));
+    int* scnt = smem_i + ((vt * T + 3) & ~3);                  // live entries per voxel
+    float* srow = reinterpret_cast<float*>(scnt + ((vt + 3) & ~3));
     int* gb = p.bucket + ((size_t)f * p.cap + v0) * T;
     for (int e = threadIdx.x; e < E; e += kBlock) {
         sidx[e] = gb[e];
         gb[e] = kEmptyIdx;
     }
-    if (T > kChainMaxT)
-        for (int v = threadIdx.x; v < nv; v += kBlock) p.cnt[(size_t)f * p.cap + v0 + v] = 0;
-    __syncthreads();
+    if (T > kChainMaxT) {
+        // count + bucket path: the counter says how many points the voxel saw; the live
+        // entries are the first min(count, T) positions of its bucket, in arrival order
+        for (int v = threadIdx.x; v < nv; v += kBlock) {
+            int* c = p.cnt + (size_t)f * p.cap + v0 + v;
+            scnt[v] = min(*c, T);
+            *c = 0;
+        }
+        __syncthreads();
+    } else {
+        __syncthreads();
+        for (int v = threadIdx.x; v < nv; v += kBlock) {
+            int c = 0;
+            for (int k = 0; k < T; ++k) c += (sidx[v * T + k] != kEmptyIdx);
+            scnt[v] = c;
+        }
+        __syncthreads();
+    }
     const size_t gout = (size_t)p.frame_voxel_offsets[f] + v0;
     for (int e = threadIdx.x; e < E; e += kBlock) {
         const int v = e / T, s = e - v * T;
         const int my = sidx[e];
-        const int* vb = sidx + v * T;
-        int nvalid = 0, r = 0;
-        for (int k = 0; k < T; ++k) {
-            const int o = vb[k];
-            nvalid += (o != kEmptyIdx);
-            r += (o < my);
-        }
+        const int nvalid = scnt[v];
         if (my != kEmptyIdx) {
+            const int* vb = sidx + v * T;
+            int r = 0;
+            for (int k = 0; k < nvalid; ++k) r += (vb[k] < my);   // slot = rank of the index in the voxel
             float* dst = srow + (size_t)(v * T + r) * F;
             fetch_row(p, fr, my, dst);
             if (r == 0) write_coor(p, f, gout + v, cell_of(p.g, dst[0], dst[1], dst[2]));
@@ -757,9 +770,7 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
         const int C = p.mean_c;
         for (int k = threadIdx.x; k < nv * C; k += kBlock) {
             const int v = k / C, c = k - v * C;
-            const int* vb = sidx + v * T;
-            int nvalid = 0;
-            for (int j = 0; j < T; ++j) nvalid += (vb[j] != kEmptyIdx);
+            const int nvalid = scnt[v];
             float s = 0.0f;
             for (int j = 0; j < T; ++j) s = __fadd_rn(s, srow[(size_t)(v * T + j) * F + c]);
             p.mean_out[(gout + v) * C + c] = __fdiv_rn(s, (float)nvalid);
