@@ -567,7 +567,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         launch_k(h, k_verify, dim3(std::max(chunks, 1), B), kBlock, 0, st, p);
     }
     if (chunks > 0) {
-        { ProfScope ps(h, 3, st); launch_k(h, k_slot, dim3(std::min(chunks, std::max(32, (148 * 8 + B - 1) / B)), B), kBlock, 0, st, p); }
+        { ProfScope ps(h, 3, st); const int sgx = p.overflow_continue ? chunks : 48;   // measured: break is flat from 32 to 64, continue wants all chunks
+          launch_k(h, k_slot, dim3(std::min(chunks, std::max(sgx, (148 * 8 + B - 1) / B)), B), kBlock, 0, st, p); }
         if (T > kChainMaxT) {
             const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
             ProfScope ps(h, 4, st);

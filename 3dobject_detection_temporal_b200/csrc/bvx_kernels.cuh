@@ -375,18 +375,32 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, i
         p.state[f].n_done = eff;
         if (!cut) p.state[f].istar = eff;
     }
-    if (cut && cut_chunk >= 0) {
-        // the point that would open voxel #cap: (cap - prefix)-th first occurrence of this chunk
-        int need = cap - cut_base;
-        const int w0 = fr.word_off + cut_chunk * kChunkWords;
-        const int nw = min(kChunkWords, nwords - cut_chunk * kChunkWords);
-        int w = 0;
-        for (; w + 1 < nw; ++w)
-            if (__ldcg(p.wordlocal + w0 + w + 1) > need) break;
-        need -= __ldcg(p.wordlocal + w0 + w);
-        unsigned int m = __ldcg(p.first + w0 + w);
-        for (; need > 0; --need) m &= m - 1;
-        p.state[f].istar = (cut_chunk * kChunkWords + w) * 32 + (__ffs(m) - 1);
+    {
+        // The point that would open voxel #cap: the (cap - prefix)-th first occurrence of the cut
+        // chunk.  At most one thread found that chunk; broadcast it, then warp 0 searches the
+        // chunk's 32 words with one load per lane.
+        __shared__ int s_cut[2];
+        if (threadIdx.x == 0) s_cut[0] = -1;
+        __syncthreads();
+        if (cut_chunk >= 0) { s_cut[0] = cut_chunk; s_cut[1] = cut_base; }
+        __syncthreads();
+        if (cut && s_cut[0] >= 0 && threadIdx.x < 32) {
+            const int cc = s_cut[0];
+            int need = cap - s_cut[1];
+            const int w0 = fr.word_off + cc * kChunkWords;
+            const int nw = min(kChunkWords, nwords - cc * kChunkWords);
+            const int lane = threadIdx.x;
+            // word w holds the target iff wordlocal[w] <= need < wordlocal[w + 1]; 32 words, one per lane
+            const int lo = lane < nw ? __ldcg(p.wordlocal + w0 + lane) : 0x7FFFFFFF;
+            const unsigned int le = __ballot_sync(0xffffffffu, lo <= need);
+            const int w = 31 - __clz(le);                  // last word whose prefix is <= need (word 0 always is)
+            if (lane == w) {
+                need -= lo;
+                unsigned int m = __ldcg(p.first + w0 + w);
+                for (; need > 0; --need) m &= m - 1;
+                p.state[f].istar = (cc * kChunkWords + w) * 32 + (__ffs(m) - 1);
+            }
+        }
     }
     __threadfence();
     __syncthreads();
