@@ -69,6 +69,9 @@ SYMBOLS = {
                                                  _vp, _vp, _vp]),
     "bvx_host_alloc": (ctypes.c_int, [ctypes.POINTER(_vp), ctypes.c_size_t]),
     "bvx_host_free": (ctypes.c_int, [_vp]),
+    "bvx_set_prefix_upload": (ctypes.c_int, [_vp, _i32]),
+    "bvx_last_transfer": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64),
+                                         ctypes.POINTER(_i32)]),
     "bvx_mean_vfe": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_scatter_bev": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_anchors_area_workspace_bytes": (ctypes.c_size_t, [_i32, _i32, _i32, _i32, _i32]),

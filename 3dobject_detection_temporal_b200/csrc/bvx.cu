@@ -69,6 +69,12 @@ struct bvx_handle {
     std::vector<cudaEvent_t> ev_h2d, ev_done;
     int32_t* pin_offs = nullptr;
     size_t pin_offs_count = 0;
+    FrameState* pin_state = nullptr;   // per-frame results of the last pipelined host call
+    size_t pin_state_count = 0;
+    bool prefix_upload = true;         // break mode: upload only the prefix of a frame the cut-off can reach
+    float cut_ratio = 0.f;             // largest (cut-off index / points) over the frames of the last call; 0 = unknown
+    unsigned long long last_h2d = 0, last_d2h = 0;   // bytes moved by the last host-form call
+    int last_redo = 0;                 // sub-batches of the last call that had to be redone with full frames
     // host-form staging
     void* stage_in = nullptr;
     size_t stage_in_bytes = 0;
@@ -207,6 +213,7 @@ extern "C" int bvx_destroy(bvx_handle* h)
     for (cudaEvent_t e : h->ev_h2d) cudaEventDestroy(e);
     for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
     if (h->pin_offs) cudaFreeHost(h->pin_offs);
+    if (h->pin_state) cudaFreeHost(h->pin_state);
     if (h->stage_in) cudaFreeHost(h->stage_in);
     if (h->stage_out) cudaFreeHost(h->stage_out);
     for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
@@ -702,12 +709,7 @@ static int stage_in(bvx_handle* h, const void* src, size_t bytes, cudaStream_t s
         return BVX_OK;
     }
     if (bytes > h->stage_in_bytes) {
-        if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
-    if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
-    for (cudaEvent_t e : h->ev_h2d) cudaEventDestroy(e);
-    for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
-    if (h->pin_offs) cudaFreeHost(h->pin_offs);
-    if (h->stage_in) cudaFreeHost(h->stage_in);
+        if (h->stage_in) cudaFreeHost(h->stage_in);
         h->stage_in = nullptr;
         CK(h, cudaMallocHost(&h->stage_in, bytes));
         h->stage_in_bytes = bytes;
@@ -756,6 +758,31 @@ static int stage_out(bvx_handle* h, void* dst[3], const void* src[3], const size
 // sub-batch k-1 overlap, so the call costs about max(H2D, D2H) on the full-duplex PCIe link
 // instead of H2D + kernels + D2H.  Results land in the caller's buffers exactly as in the
 // unpipelined form (concatenated in frame order, global batch index in the coordinates).
+// Kernels of sub-batch k (frames [f0, f1), the first pre[f] points of each) on st, then the
+// D2H of its offsets and per-frame state into the pinned mirrors.
+static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::vector<int>& pre, int f0, int f1,
+                               int k, int fs, int f, int cap, cudaStream_t st)
+{
+    const int T = h->cfg.max_num_points;
+    const int bk = f1 - f0;
+    std::vector<bvx_sweep> sw(bk);
+    std::vector<FrameSpec> fr(bk);
+    for (int i = 0; i < bk; ++i) {
+        sw[i] = plain_sweep(h->dev_points + (size_t)offs[f0 + i] * f, pre[f0 + i]);
+        fr[i] = FrameSpec{&sw[i], 1, 0};
+    }
+    const size_t v0 = (size_t)f0 * cap;
+    Outputs o{h->dev_voxels + v0 * T * f, h->dev_coors + v0 * 4, h->dev_num + v0,
+              h->dev_offs_sub + (size_t)k * (fs + 1), nullptr, nullptr, 0, 4, f0};
+    int rc = run_pipeline(h, fr, f, f, cap, o, st);
+    if (rc) return rc;
+    CK(h, cudaMemcpyAsync(h->pin_offs + (size_t)k * (fs + 1), h->dev_offs_sub + (size_t)k * (fs + 1),
+                          ((size_t)bk + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CK(h, cudaMemcpyAsync(h->pin_state + f0, h->d_state, (size_t)bk * sizeof(FrameState), cudaMemcpyDeviceToHost, st));
+    h->last_d2h += ((size_t)bk + 1) * 4 + (size_t)bk * sizeof(FrameState);
+    return BVX_OK;
+}
+
 static int generate_batched_pipelined(bvx_handle* h, const float* points, const int32_t* offs, int b, int f,
                                       int cap, float* voxels, int32_t* coors4, int32_t* num_points,
                                       int32_t* fvo_host, cudaStream_t st)
@@ -783,37 +810,58 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         CK(h, cudaMallocHost((void**)&h->pin_offs, need * 4));
         h->pin_offs_count = need;
     }
+    if ((size_t)b > h->pin_state_count) {
+        if (h->pin_state) cudaFreeHost(h->pin_state);
+        h->pin_state = nullptr;
+        CK(h, cudaMallocHost((void**)&h->pin_state, (size_t)b * sizeof(FrameState)));
+        h->pin_state_count = (size_t)b;
+    }
+    // Break mode: nothing after the cut-off point i* of a frame can reach the output (the
+    // reference's loop stops there), so only a prefix of each frame is uploaded -- as long as the
+    // last call's cut-offs say where i* is likely to be (x 1.25 + one chunk).  The frame's own
+    // result says whether the prefix was enough (more distinct cells than max_voxels inside it);
+    // if not, the rest of the frame follows and the sub-batch is redone.  Results are exact either way.
+    const bool brk = h->cfg.overflow_mode == BVX_OVERFLOW_BREAK;
+    const bool spec = brk && h->prefix_upload && h->cut_ratio > 0.f && h->cut_ratio * 1.25f < 0.9f;
+    std::vector<int> pre(b);
+    for (int i = 0; i < b; ++i) {
+        const int n = offs[i + 1] - offs[i];
+        pre[i] = n;
+        if (spec) {
+            const long long want = ((long long)std::ceil((double)n * h->cut_ratio * 1.25) / kChunk + 2) * kChunk;
+            pre[i] = (int)std::min<long long>(n, want);
+        }
+    }
     // the copy streams start after whatever the caller queued on its stream
     CK(h, cudaEventRecord(h->ev_done[ns], st));
     CK(h, cudaStreamWaitEvent(h->s_h2d, h->ev_done[ns], 0));
     // leg 1: every H2D copy, back to back on the copy-in stream
     for (int k = 0; k < ns; ++k) {
         const int f0 = k * fs, f1 = std::min(b, f0 + fs);
-        const size_t p0 = (size_t)offs[f0], p1 = (size_t)offs[f1];
-        if (p1 > p0)
-            CK(h, cudaMemcpyAsync(h->dev_points + p0 * f, points + p0 * f, (p1 - p0) * f * 4,
-                                  cudaMemcpyHostToDevice, h->s_h2d));
+        if (!spec) {
+            const size_t p0 = (size_t)offs[f0], p1 = (size_t)offs[f1];
+            if (p1 > p0) {
+                CK(h, cudaMemcpyAsync(h->dev_points + p0 * f, points + p0 * f, (p1 - p0) * f * 4,
+                                      cudaMemcpyHostToDevice, h->s_h2d));
+                h->last_h2d += (p1 - p0) * f * 4;
+            }
+        } else {
+            for (int i = f0; i < f1; ++i) {
+                if (pre[i] == 0) continue;
+                const size_t p0 = (size_t)offs[i];
+                CK(h, cudaMemcpyAsync(h->dev_points + p0 * f, points + p0 * f, (size_t)pre[i] * f * 4,
+                                      cudaMemcpyHostToDevice, h->s_h2d));
+                h->last_h2d += (size_t)pre[i] * f * 4;
+            }
+        }
         CK(h, cudaEventRecord(h->ev_h2d[k], h->s_h2d));
     }
     // leg 2: the kernels of each sub-batch on the caller's stream, outputs at capacity stride
-    std::vector<int32_t> loc(fs + 1);
     for (int k = 0; k < ns; ++k) {
-        const int f0 = k * fs, f1 = std::min(b, f0 + fs), bk = f1 - f0;
-        for (int i = 0; i <= bk; ++i) loc[i] = offs[f0 + i] - offs[f0];
+        const int f0 = k * fs, f1 = std::min(b, f0 + fs);
         CK(h, cudaStreamWaitEvent(st, h->ev_h2d[k], 0));
-        std::vector<bvx_sweep> sw(bk);
-        std::vector<FrameSpec> fr(bk);
-        for (int i = 0; i < bk; ++i) {
-            sw[i] = plain_sweep(h->dev_points + (size_t)offs[f0 + i] * f, loc[i + 1] - loc[i]);
-            fr[i] = FrameSpec{&sw[i], 1, 0};
-        }
-        const size_t v0 = (size_t)f0 * cap;
-        Outputs o{h->dev_voxels + v0 * T * f, h->dev_coors + v0 * 4, h->dev_num + v0,
-                  h->dev_offs_sub + (size_t)k * (fs + 1), nullptr, nullptr, 0, 4, f0};
-        int rc = run_pipeline(h, fr, f, f, cap, o, st);
+        int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, st);
         if (rc) return rc;
-        CK(h, cudaMemcpyAsync(h->pin_offs + (size_t)k * (fs + 1), h->dev_offs_sub + (size_t)k * (fs + 1),
-                              ((size_t)bk + 1) * 4, cudaMemcpyDeviceToHost, st));
         CK(h, cudaEventRecord(h->ev_done[k], st));
     }
     // leg 3: as each sub-batch finishes, its M rows go home on the copy-out stream
@@ -822,6 +870,25 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
     for (int k = 0; k < ns; ++k) {
         const int f0 = k * fs, f1 = std::min(b, f0 + fs), bk = f1 - f0;
         CK(h, cudaEventSynchronize(h->ev_done[k]));
+        bool redo = false;
+        for (int i = f0; i < f1; ++i)
+            if (pre[i] < offs[i + 1] - offs[i] && !(h->pin_state[i].total > cap)) redo = true;
+        if (redo) {
+            // a prefix held no cut-off: bring the rest of the short frames and run the sub-batch again
+            for (int i = f0; i < f1; ++i) {
+                const int n = offs[i + 1] - offs[i];
+                if (pre[i] == n) continue;
+                const size_t p0 = (size_t)offs[i] + pre[i];
+                CK(h, cudaMemcpyAsync(h->dev_points + p0 * f, points + p0 * f, (size_t)(n - pre[i]) * f * 4,
+                                      cudaMemcpyHostToDevice, st));
+                h->last_h2d += (size_t)(n - pre[i]) * f * 4;
+                pre[i] = n;
+            }
+            int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, st);
+            if (rc) return rc;
+            CK(h, cudaStreamSynchronize(st));
+            h->last_redo += 1;
+        }
         const int32_t* lo = h->pin_offs + (size_t)k * (fs + 1);
         const size_t m = (size_t)lo[bk], v0 = (size_t)f0 * cap;
         for (int i = 1; i <= bk; ++i) fvo_host[f0 + i] = (int32_t)(run + (size_t)lo[i]);
@@ -830,8 +897,22 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
                                   cudaMemcpyDeviceToHost, h->s_d2h));
             CK(h, cudaMemcpyAsync(coors4 + run * 4, h->dev_coors + v0 * 4, m * 16, cudaMemcpyDeviceToHost, h->s_d2h));
             CK(h, cudaMemcpyAsync(num_points + run, h->dev_num + v0, m * 4, cudaMemcpyDeviceToHost, h->s_d2h));
+            h->last_d2h += m * ((size_t)T * f * 4 + 16 + 4);
         }
         run += m;
+    }
+    // where the cut-offs were this time: the next call's prefix
+    if (brk) {
+        float r = 0.f;
+        bool any = false;
+        for (int i = 0; i < b; ++i) {
+            const int n = offs[i + 1] - offs[i];
+            if (n == 0) continue;
+            any = true;
+            const FrameState& s = h->pin_state[i];
+            r = std::max(r, s.total > cap ? (float)(s.istar + 1) / (float)n : 1.0f);
+        }
+        if (any) h->cut_ratio = r;
     }
     CK(h, cudaStreamSynchronize(h->s_d2h));
     return BVX_OK;
@@ -850,6 +931,7 @@ extern "C" int bvx_generate_batched_host(bvx_handle* h, const float* points, con
     const size_t n = (size_t)offs[b];
     int rc = ensure_host_buffers(h, n * f * 4, (size_t)cap * b, T * f);
     if (rc) return rc;
+    h->last_h2d = 0; h->last_d2h = 0; h->last_redo = 0;
     if (b >= 2 && n > 0 && is_pinned(points) && is_pinned(voxels) && is_pinned(coors4) && is_pinned(num_points))
         return generate_batched_pipelined(h, points, offs, b, f, cap, voxels, coors4, num_points, fvo_host, st);
     if ((rc = stage_in(h, points, n * f * 4, st))) return rc;
@@ -862,6 +944,8 @@ extern "C" int bvx_generate_batched_host(bvx_handle* h, const float* points, con
     void* dst[3] = {voxels, coors4, num_points};
     const void* src[3] = {h->dev_voxels, h->dev_coors, h->dev_num};
     const size_t bytes[3] = {m * T * f * 4, m * 16, m * 4};
+    h->last_h2d = n * f * 4;
+    h->last_d2h = bytes[0] + bytes[1] + bytes[2] + ((size_t)b + 1) * 4;
     return stage_out(h, dst, src, bytes, st);
 }
 
@@ -886,7 +970,27 @@ extern "C" int bvx_generate_host(bvx_handle* h, const float* points, int32_t n, 
     void* dst[3] = {voxels, coors, num_points};
     const void* src[3] = {h->dev_voxels, h->dev_coors, h->dev_num};
     const size_t bytes[3] = {m * T * f * 4, m * 12, m * 4};
+    h->last_h2d = (size_t)n * f * 4;
+    h->last_d2h = bytes[0] + bytes[1] + bytes[2] + 4;
+    h->last_redo = 0;
     return stage_out(h, dst, src, bytes, st);
+}
+
+extern "C" int bvx_set_prefix_upload(bvx_handle* h, int32_t on)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    h->prefix_upload = on != 0;
+    h->cut_ratio = 0.f;
+    return BVX_OK;
+}
+
+extern "C" int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes, uint64_t* d2h_bytes, int32_t* redone)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (h2d_bytes) *h2d_bytes = h->last_h2d;
+    if (d2h_bytes) *d2h_bytes = h->last_d2h;
+    if (redone) *redone = h->last_redo;
+    return BVX_OK;
 }
 
 // ------------------------------------------------------------------ profiling

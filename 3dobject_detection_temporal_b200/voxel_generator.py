@@ -34,7 +34,7 @@ def _is_torch(x):
 
 class VoxelGenerator:
     def __init__(self, voxel_size, point_cloud_range, max_num_points, max_voxels=20000,
-                 overflow="break", grid="hashed", device=None):
+                 overflow="break", grid="hashed", device=None, prefix_upload=True):
         if overflow not in _lib.OVERFLOW:
             raise ValueError(f"overflow must be 'break' or 'continue', got {overflow!r}")
         if grid not in _lib.GRID:
@@ -48,6 +48,7 @@ class VoxelGenerator:
         self._overflow = overflow
         self._grid = grid
         self._device = device
+        self._prefix_upload = bool(prefix_upload)
         lib = _lib.load()
         gs = (ctypes.c_int64 * 3)()
         _lib.check(lib.bvx_grid_size(
@@ -120,6 +121,8 @@ class VoxelGenerator:
         cfg.device = dev
         h = ctypes.c_void_p()
         _lib.check(_lib.load().bvx_create(ctypes.byref(cfg), ctypes.byref(h)))
+        if not self._prefix_upload:
+            _lib.check(_lib.load().bvx_set_prefix_upload(h, 0), h)
         self._handle = h
         self._cap = cap
         return h
@@ -141,6 +144,15 @@ class VoxelGenerator:
         out = ctypes.c_size_t()
         _lib.check(_lib.load().bvx_workspace_bytes(self._handle, ctypes.byref(out)), self._handle)
         return int(out.value)
+
+    def last_transfer(self):
+        """(h2d_bytes, d2h_bytes, sub_batches_redone) of the last numpy (host form) call."""
+        if self._handle is None:
+            return 0, 0, 0
+        a, b, r = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_int32()
+        _lib.check(_lib.load().bvx_last_transfer(self._handle, ctypes.byref(a), ctypes.byref(b), ctypes.byref(r)),
+                   self._handle)
+        return int(a.value), int(b.value), int(r.value)
 
     def profile(self, on=True):
         """Per-kernel device timing (CUDA events around every launch) on/off."""

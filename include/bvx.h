@@ -157,6 +157,20 @@ int bvx_generate_batched_host(bvx_handle* h, const float* points_host,
 int bvx_host_alloc(void** out, size_t bytes);  /* pinned host memory */
 int bvx_host_free(void* p);
 
+/* Pinned batched host form, BVX_OVERFLOW_BREAK: nothing after a frame's cut-off
+ * point (the point that would open voxel number max_voxels) can reach the
+ * output -- the reference's loop stops reading there -- so only a prefix of
+ * each frame is copied to the device: 1.25 x the largest cut-off fraction seen
+ * in the previous call on this handle, plus two chunks (the first call copies
+ * everything).  Each frame's own result tells whether its prefix contained the
+ * cut-off; if not, the rest of the frame is copied and its sub-batch is run
+ * again, so results never depend on the guess.  On by default.
+ * bvx_last_transfer: bytes copied each way by the last *_host call on the
+ * handle and how many sub-batches had to be run again. */
+int bvx_set_prefix_upload(bvx_handle* h, int32_t on);
+int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes,
+                      uint64_t* d2h_bytes, int32_t* redone);
+
 /* Replaces VoxelFeatureExtractorV3.forward(features, num_voxels)
  * (second/pytorch/models/voxel_encoder.py:201-206): out[v, c] =
  * sum_t voxels[v, t, c] / num_points[v] for c < c_out.  The reference

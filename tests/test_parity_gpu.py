@@ -224,6 +224,89 @@ def test_batched_host_pipelined(pkg, oracle, synth, overflow):
             _eq((hv, hc, hn), (wv, wc, wn), f"pipelined host {sizes[:3]}")
 
 
+def _pinned_batch(pkg, frames, cap, T=5):
+    cat = np.concatenate(frames, axis=0)
+    offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
+    hp = pkg.pinned_empty(cat.shape, np.float32)
+    hp[:] = cat
+    b = len(frames)
+    out = (pkg.pinned_empty((b * cap, T, 4), np.float32), pkg.pinned_empty((b * cap, 4), np.int32),
+           pkg.pinned_empty((b * cap,), np.int32), pkg.pinned_empty((b + 1,), np.int32))
+    return hp, offs, out
+
+
+def test_prefix_upload_is_exact(pkg, oracle, synth):
+    """Break mode, pinned batches: after the first call only a prefix of each frame is uploaded
+    (sized from the previous call's cut-offs).  Results must equal the oracle's whether the guess
+    holds (later calls on similar frames), fails for every frame (a call whose cap is never
+    reached) or fails for some frames of a sub-batch (mixed batch)."""
+    cap = 1500
+    g, o = _pair(pkg, oracle, KITTI, 5, cap)
+    early = [synth.lidar_frame(30000, "kitti", seed=300 + i) for i in range(12)]      # cut-off near 10 %
+    hp, offs, out = _pinned_batch(pkg, early, cap)
+    want = o.generate_batched(early)
+    full = hp.nbytes
+    seen = []
+    for _ in range(3):
+        hv, hc, hn, hoff = g.generate_batched(hp, offs, out=out)
+        assert np.array_equal(hoff, want[3])
+        _eq((hv, hc, hn), want[:3], "prefix upload, guess holds")
+        seen.append(g.last_transfer())
+    assert seen[0][0] == full and seen[0][2] == 0                 # first call: everything
+    assert seen[1][0] < 0.5 * full and seen[1][2] == 0            # then a prefix, nothing redone
+    assert seen[2][0] == seen[1][0]
+    # same handle, frames that never reach the cap: every prefix is too short, all sub-batches redone
+    sparse = [synth.lidar_frame(30000, "kitti", seed=400 + i)[::40].copy() for i in range(12)]
+    sparse = [np.ascontiguousarray(np.repeat(f, 40, axis=0)[:30000]) for f in sparse]  # 750 distinct points each
+    hp2, offs2, out2 = _pinned_batch(pkg, sparse, cap)
+    want2 = o.generate_batched(sparse)
+    assert want2[3][-1] < 12 * cap                                  # (no frame is cut)
+    hv, hc, hn, hoff = g.generate_batched(hp2, offs2, out=out2)
+    assert np.array_equal(hoff, want2[3])
+    _eq((hv, hc, hn), want2[:3], "prefix upload, guess fails everywhere")
+    h2d, _, redone = g.last_transfer()
+    assert redone > 0 and h2d == hp2.nbytes                         # the rest of each frame followed
+    # the guess is now 'no cut-off': the next call uploads everything again and redoes nothing
+    hv, hc, hn, hoff = g.generate_batched(hp, offs, out=out)
+    _eq((hv, hc, hn), want[:3], "back to cut frames")
+    assert g.last_transfer()[0] == full and g.last_transfer()[2] == 0
+    g.generate_batched(hp, offs, out=out)                           # learn the early cut-off again
+    # mixed batch: cut and uncut frames side by side in one sub-batch
+    mixed = [early[0], sparse[0], early[1], sparse[1], sparse[2], early[2], early[3], sparse[3], early[4]]
+    hp3, offs3, out3 = _pinned_batch(pkg, mixed, cap)
+    want3 = o.generate_batched(mixed)
+    hv, hc, hn, hoff = g.generate_batched(hp3, offs3, out=out3)
+    assert np.array_equal(hoff, want3[3])
+    _eq((hv, hc, hn), want3[:3], "prefix upload, mixed batch")
+    assert g.last_transfer()[2] > 0
+    # switched off: always the whole frame
+    g2 = pkg.VoxelGenerator(KITTI["voxel_size"], KITTI["point_cloud_range"], 5, cap, prefix_upload=False)
+    for _ in range(2):
+        hv, hc, hn, hoff = g2.generate_batched(hp, offs, out=out)
+        assert g2.last_transfer()[0] == full
+    _eq((hv, hc, hn), want[:3], "prefix upload off")
+
+
+def test_pageable_after_pinned_keeps_streams(pkg, oracle, synth):
+    """Growing the pageable staging buffer must not disturb the pipelined form's streams and events."""
+    cap = 1500
+    g, o = _pair(pkg, oracle, KITTI, 5, cap)
+    frames = [synth.lidar_frame(6000, "kitti", seed=500 + i) for i in range(5)]
+    hp, offs, out = _pinned_batch(pkg, frames, cap)
+    want = o.generate_batched(frames)
+    _eq(g.generate_batched(hp, offs, out=out)[:3], want[:3], "pinned first")
+    same = np.concatenate(frames, axis=0)                           # pageable, same handle: staging buffer is created
+    _eq(g.generate_batched(same, offs)[:3], want[:3], "pageable, same handle")
+    _eq(g.generate_batched(hp, offs, out=out)[:3], want[:3], "pinned after pageable")
+    big = np.concatenate(frames + frames, axis=0)                   # pageable, larger than anything staged so far
+    offs_big = np.concatenate([[0], np.cumsum([6000] * 10)]).astype(np.int32)
+    wb = o.generate_batched(frames + frames)
+    _eq(g.generate_batched(big, offs_big)[:3], wb[:3], "pageable, staging buffer grows")
+    hp, offs, out = _pinned_batch(pkg, frames, cap)                 # (the handle may have been re-created: fresh buffers)
+    _eq(g.generate_batched(hp, offs, out=out)[:3], want[:3], "pinned again")
+    _eq(g.generate_batched(hp, offs, out=out)[:3], want[:3], "pinned again, second call")
+
+
 def test_handle_growth_and_reuse(pkg, oracle, synth):
     g, o = _pair(pkg, oracle, KITTI, 5, 2000)
     for n in (1000, 50000, 200, 80000, 50000):
