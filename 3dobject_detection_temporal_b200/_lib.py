@@ -63,6 +63,8 @@ SYMBOLS = {
                                            _vp, _vp]),
     "bvx_generate_batched": (ctypes.c_int, [_vp, _vp, ctypes.POINTER(_i32), _i32, _i32, _i32, _vp, _vp, _vp,
                                             _vp, _vp, _i32, _vp]),
+    "bvx_generate_batched_sweeps": (ctypes.c_int, [_vp, ctypes.POINTER(BvxSweep), ctypes.POINTER(_i32), _i32, _i32,
+                                                   _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp]),
     "bvx_generate_host": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, ctypes.POINTER(_i32),
                                          _vp]),
     "bvx_generate_batched_host": (ctypes.c_int, [_vp, _vp, ctypes.POINTER(_i32), _i32, _i32, _i32, _vp, _vp,

@@ -669,6 +669,25 @@ extern "C" int bvx_generate_batched(bvx_handle* h, const float* points, const in
     return run_pipeline(h, fr, f, f, max_voxels, o, (cudaStream_t)stream);
 }
 
+extern "C" int bvx_generate_batched_sweeps(bvx_handle* h, const bvx_sweep* sweeps, const int32_t* sweep_offsets,
+                                           int32_t b, int32_t f_in, int32_t append_dt, int32_t max_voxels,
+                                           float* voxels, int32_t* coors4, int32_t* num_points,
+                                           int32_t* frame_voxel_offsets, float* mean, int32_t mean_c, void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (b < 1 || !sweep_offsets || !sweeps) return fail(h, BVX_ERR_BAD_ARGUMENT, "need sweeps, sweep_offsets and b >= 1");
+    if (f_in < 3) return fail(h, BVX_ERR_BAD_ARGUMENT, "points need at least 3 features, got %d", f_in);
+    if (sweep_offsets[0] != 0) return fail(h, BVX_ERR_BAD_ARGUMENT, "sweep_offsets must start at 0");
+    std::vector<FrameSpec> fr(b);
+    for (int i = 0; i < b; ++i) {
+        const int k = sweep_offsets[i + 1] - sweep_offsets[i];
+        if (k < 1) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d has no sweep", i);
+        fr[i] = FrameSpec{sweeps + sweep_offsets[i], k, append_dt ? 1 : 0};
+    }
+    Outputs o{voxels, coors4, num_points, frame_voxel_offsets, nullptr, mean, mean_c, 4, 0};
+    return run_pipeline(h, fr, f_in, f_in + (append_dt ? 1 : 0), max_voxels, o, (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------ host forms
 static bool is_pinned(const void* p)
 {

@@ -233,7 +233,28 @@ class VoxelGenerator:
         else:
             dev = torch.device("cuda", self._device_index())
         keep, arr = [], (_lib.BvxSweep * len(sweeps))()
-        f_in = None
+        f_in, total = self._sweep_structs(sweeps, arr, 0, dev, use_torch, keep, None)
+        f_out = f_in + 1
+        h = self._ensure(total, 1, max_voxels, f_out, dev.index)
+        tt = self._max_num_points
+        with torch.cuda.device(dev):
+            voxels = torch.empty((max_voxels, tt, f_out), dtype=torch.float32, device=dev)
+            coors = torch.empty((max_voxels, 3), dtype=torch.int32, device=dev)
+            num = torch.empty((max_voxels,), dtype=torch.int32, device=dev)
+            cnt = torch.empty((1,), dtype=torch.int32, device=dev)
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(_lib.load().bvx_generate_sweeps(
+                h, arr, len(sweeps), f_in, max_voxels, voxels.data_ptr(), coors.data_ptr(),
+                num.data_ptr(), cnt.data_ptr(), st), h)
+            m = int(cnt.item())
+        out = voxels[:m], coors[:m], num[:m]
+        if not use_torch:
+            out = tuple(o.cpu().numpy() for o in out)
+        return out
+
+    def _sweep_structs(self, sweeps, arr, base, dev, use_torch, keep, f_in):
+        """Fill arr[base:base+len(sweeps)]; returns (f_in, points in these sweeps)."""
+        import torch
         total = 0
         for i, (pts, R, t, dt) in enumerate(sweeps):
             if use_torch:
@@ -249,29 +270,58 @@ class VoxelGenerator:
             elif f_in != p.shape[1]:
                 raise ValueError("all sweeps need the same feature count")
             keep.append(p)
-            arr[i].points = p.data_ptr()
-            arr[i].n = int(p.shape[0])
-            arr[i].has_transform = 0 if R is None else 1
+            a = arr[base + i]
+            a.points = p.data_ptr()
+            a.n = int(p.shape[0])
+            a.has_transform = 0 if (R is None and t is None) else 1
             Rm = np.eye(3, dtype=np.float32) if R is None else np.asarray(R, dtype=np.float32).reshape(3, 3)
             tv = np.zeros(3, dtype=np.float32) if t is None else np.asarray(t, dtype=np.float32).reshape(3)
-            arr[i].R[:] = Rm.reshape(-1).tolist()
-            arr[i].t[:] = tv.tolist()
-            arr[i].dt = float(np.float32(dt))
+            a.R[:] = Rm.reshape(-1).tolist()
+            a.t[:] = tv.tolist()
+            a.dt = float(np.float32(dt))
             total += int(p.shape[0])
-        f_out = f_in + 1
-        h = self._ensure(total, 1, max_voxels, f_out, dev.index)
-        tt = self._max_num_points
+        return f_in, total
+
+    def generate_batched_sweeps(self, frames, max_voxels=None, append_dt=True, mean_channels=0):
+        """B frames, each a list of sweeps ``(points[N_s, F_in], R or None, t or None, dt)``, key frame
+        first: the batched form of ``generate_sweeps``.  ``append_dt=False`` keeps F_out = F_in; with
+        one transformed sweep per frame that is the reference's global rotation / scaling / flip
+        (second/core/preprocess.py:756-804) applied in registers while the points are loaded.
+        Returns ``(voxels [sum M, T, F_out], coors [sum M, 4], num_points, frame_voxel_offsets
+        [B + 1][, mean])`` -- CUDA tensors for CUDA input, numpy arrays for numpy input."""
+        import torch
+        max_voxels = int(max_voxels or self._max_voxels)
+        b = len(frames)
+        if b < 1 or any(len(fr) < 1 for fr in frames):
+            raise ValueError("need at least one frame and one sweep per frame")
+        use_torch = _is_torch(frames[0][0][0])
+        dev = frames[0][0][0].device if use_torch else torch.device("cuda", self._device_index())
+        nsw = sum(len(fr) for fr in frames)
+        arr = (_lib.BvxSweep * nsw)()
+        so = np.zeros(b + 1, dtype=np.int32)
+        keep, f_in, total, base = [], None, 0, 0
+        for i, fr in enumerate(frames):
+            f_in, n = self._sweep_structs(fr, arr, base, dev, use_torch, keep, f_in)
+            total += n
+            base += len(fr)
+            so[i + 1] = base
+        f_out = f_in + (1 if append_dt else 0)
+        h = self._ensure(total, max(b, nsw), max_voxels, f_out, dev.index)
+        tt, cap = self._max_num_points, b * max_voxels
         with torch.cuda.device(dev):
-            voxels = torch.empty((max_voxels, tt, f_out), dtype=torch.float32, device=dev)
-            coors = torch.empty((max_voxels, 3), dtype=torch.int32, device=dev)
-            num = torch.empty((max_voxels,), dtype=torch.int32, device=dev)
-            cnt = torch.empty((1,), dtype=torch.int32, device=dev)
+            voxels = torch.empty((cap, tt, f_out), dtype=torch.float32, device=dev)
+            coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
+            num = torch.empty((cap,), dtype=torch.int32, device=dev)
+            fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
+            mean = (torch.empty((cap, mean_channels), dtype=torch.float32, device=dev)
+                    if mean_channels > 0 else None)
             st = torch.cuda.current_stream(dev).cuda_stream
-            _lib.check(_lib.load().bvx_generate_sweeps(
-                h, arr, len(sweeps), f_in, max_voxels, voxels.data_ptr(), coors.data_ptr(),
-                num.data_ptr(), cnt.data_ptr(), st), h)
-            m = int(cnt.item())
-        out = voxels[:m], coors[:m], num[:m]
+            _lib.check(_lib.load().bvx_generate_batched_sweeps(
+                h, arr, so.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), b, f_in, 1 if append_dt else 0,
+                max_voxels, voxels.data_ptr(), coors.data_ptr(), num.data_ptr(), fvo.data_ptr(),
+                mean.data_ptr() if mean is not None else None, mean_channels, st), h)
+            m = int(fvo[-1].item())
+        out = (voxels[:m], coors[:m], num[:m], fvo) + ((mean[:m],) if mean is not None else ())
         if not use_torch:
             out = tuple(o.cpu().numpy() for o in out)
         return out

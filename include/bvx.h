@@ -140,6 +140,24 @@ int bvx_generate_batched(bvx_handle* h, const float* points,
                          float* mean_features, int32_t mean_channels,
                          void* stream);
 
+/* B frames of k_b sweeps each: the temporal input of the north star, batched.
+ * Frame i is sweeps [sweep_offsets_host[i], sweep_offsets_host[i+1]) of
+ * sweeps_host, key frame first; rows of one frame are the concatenation of its
+ * sweeps, each transformed in registers (bvx_sweep above), never written to
+ * memory.  append_dt != 0 appends the sweep's dt as channel f_in (f_out =
+ * f_in + 1); append_dt == 0 keeps f_out = f_in -- with one transformed sweep
+ * per frame this is the global rotation / scaling / flip of the reference's
+ * augmentation (second/core/preprocess.py:756-804) fused into the point load.
+ * Outputs as bvx_generate_batched with f = f_out. */
+int bvx_generate_batched_sweeps(bvx_handle* h, const bvx_sweep* sweeps_host,
+                                const int32_t* sweep_offsets_host, int32_t b,
+                                int32_t f_in, int32_t append_dt,
+                                int32_t max_voxels, float* voxels,
+                                int32_t* coors4, int32_t* num_points,
+                                int32_t* frame_voxel_offsets,
+                                float* mean_features, int32_t mean_channels,
+                                void* stream);
+
 /* Host-buffer forms (numpy in, numpy out -- the exact shape of the reference's
  * CPU call).  Copies H2D, runs the device path, copies the M result rows D2H,
  * synchronises the stream and returns M in *voxel_num_host.  Pinned buffers

@@ -171,7 +171,7 @@ def merge_sweeps(sweeps):
         out = np.empty((n, f_in + 1), dtype=np.float32)
         has = R is not None
         Rm = np.ascontiguousarray(R if has else np.eye(3), dtype=np.float32)
-        tv = np.ascontiguousarray(t if has else np.zeros(3), dtype=np.float32)
+        tv = np.ascontiguousarray(t if (has and t is not None) else np.zeros(3), dtype=np.float32)
         _lib().orc_transform_sweep(_p(pts, _f32p), n, f_in, _p(Rm, _f32p), _p(tv, _f32p),
                                    ctypes.c_float(float(np.float32(dt))), int(has),
                                    _p(out, _f32p))

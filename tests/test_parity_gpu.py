@@ -181,6 +181,65 @@ def test_sweeps(pkg, oracle, synth, overflow):
     _eq(g.generate_sweeps(rag), o.generate(oracle.merge_sweeps(rag)), "ragged sweeps")
 
 
+def _rot_z(a):
+    c, s_ = np.cos(a), np.sin(a)
+    return np.asarray([[c, -s_, 0], [s_, c, 0], [0, 0, 1]], np.float32)
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_batched_sweeps(pkg, oracle, synth, overflow):
+    """B frames of 1-3 sweeps each (ragged, one empty sweep), dt appended: must equal the oracle run
+    on the oracle's merged clouds, frame by frame, with the batch index in the coordinates."""
+    rng = np.random.default_rng(8)
+    frames = []
+    for i, (k, n) in enumerate([(3, 9000), (1, 4000), (2, 0), (2, 12000)]):
+        sw = []
+        for j in range(k):
+            pts = synth.lidar_frame(n if not (i == 3 and j == 1) else 0, "nuscenes", seed=900 + 10 * i + j)
+            R = None if j == 0 else _rot_z(0.02 * j) @ np.eye(3, dtype=np.float32)
+            t = None if j == 0 else rng.normal(0, 0.5, 3).astype(np.float32)
+            sw.append((pts, R, t, 0.05 * j))
+        frames.append(sw)
+    for T, cap in ((5, 2500), (10, 60000)):
+        g, o = _pair(pkg, oracle, NUSC, T, cap, overflow)
+        merged = [oracle.merge_sweeps(sw) for sw in frames]
+        wv, wc, wn, woff = o.generate_batched(merged)
+        dev_frames = [[(torch.from_numpy(p).cuda(), R, t, dt) for p, R, t, dt in sw] for sw in frames]
+        for _ in range(2):
+            gv, gc, gn, goff = g.generate_batched_sweeps(dev_frames)
+            assert np.array_equal(goff.cpu().numpy(), woff)
+            _eq((gv, gc, gn), (wv, wc, wn), f"batched sweeps T={T}")
+        hv, hc, hn, hoff = g.generate_batched_sweeps(frames)              # numpy in -> numpy out
+        assert isinstance(hv, np.ndarray) and np.array_equal(hoff, woff)
+        _eq((hv, hc, hn), (wv, wc, wn), "batched sweeps, numpy")
+
+
+def test_global_augmentation_fused_into_the_load(pkg, oracle, synth):
+    """One transformed sweep per frame, no dt channel: the reference's global rotation / scaling / flip
+    (second/core/preprocess.py:756-804) applied while the points are loaded.  Voxels are bit-exact
+    against the oracle on the oracle's transformed points; the transformed coordinates themselves equal
+    numpy's in-place float32 arithmetic exactly for scaling and flip, to 1e-6 for the rotation matmul."""
+    g, o = _pair(pkg, oracle, KITTI, 5, 3000)
+    pts = [synth.lidar_frame(15000, "kitti", seed=700 + i) for i in range(3)]
+    scale = np.float32(1.0371)
+    xf = [(np.eye(3, dtype=np.float32) * scale, None),                                   # global_scaling
+          (np.diag([1, -1, 1]).astype(np.float32), None),                                # random_flip
+          (_rot_z(0.3), None)]                                                           # global_rotation
+    frames = [[(p, R, t, 0.0)] for p, (R, t) in zip(pts, xf)]
+    merged = [np.ascontiguousarray(oracle.merge_sweeps(sw)[:, :4]) for sw in frames]
+    want = o.generate_batched(merged)
+    gv, gc, gn, goff = g.generate_batched_sweeps(
+        [[(torch.from_numpy(p).cuda(), R, t, dt) for p, R, t, dt in sw] for sw in frames], append_dt=False)
+    assert gv.shape[2] == 4 and np.array_equal(goff.cpu().numpy(), want[3])
+    _eq((gv, gc, gn), want[:3], "augmentation fused into the load")
+    ref0 = pts[0].copy(); ref0[:, :3] *= float(scale)                                    # preprocess.py:759
+    ref1 = pts[1].copy(); ref1[:, 1] = -ref1[:, 1]                                       # preprocess.py:783
+    ref2 = pts[2].copy(); ref2[:, :3] = ref2[:, :3] @ _rot_z(0.3).T                      # box_np_ops rotation, axis 2
+    assert np.array_equal(np.abs(merged[0]), np.abs(ref0))       # (-0.0 vs 0.0 aside)
+    assert np.array_equal(np.abs(merged[1]), np.abs(ref1))
+    np.testing.assert_allclose(merged[2], ref2, rtol=1e-6, atol=1e-5)
+
+
 @pytest.mark.parametrize("overflow", ["break", "continue"])
 def test_batched(pkg, oracle, synth, overflow):
     sizes = [5000, 0, 33, 12001, 1, 7000]
