@@ -56,9 +56,6 @@ struct bvx_handle {
     std::vector<SegDesc> h_segs;
     std::vector<char> uploaded;  // byte image of the last uploaded layout
     bool all_plain = false;      // every frame of the current layout is one plain segment
-    long long table_used = 0;    // table entries the current layout touches
-    size_t l2_window_max = 0;    // cudaDevAttrMaxAccessPolicyWindowSize (0: persistence unavailable)
-    size_t l2_persist = 0;       // bytes of L2 set aside for persisting lines
     static const int kRing = 4;
     char* pin[kRing] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t pin_ev[kRing];
@@ -268,22 +265,6 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     };
     cudaError_t e = cudaSetDevice(h->device);
     if (e != cudaSuccess) return bail(e, "cudaSetDevice");
-    {   // L2 persistence for the hash tables: random atomics on L2-resident lines are ~5x
-        // faster than on lines that have to come back from HBM (tools/microbench.cu)
-        int maxp = 0, maxw = 0;
-        cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, h->device);
-        cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
-        // opt-in: measured no gain on B200
-        if (maxp > 0 && maxw > 0 && getenv("BVX_L2_PERSIST")) {
-            size_t cur = 0;
-            cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
-            if (cur < (size_t)maxp) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)maxp);
-            cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
-            h->l2_persist = cur;
-            h->l2_window_max = (size_t)maxw;
-        }
-        cudaGetLastError();
-    }
     const long long np = cfg->max_points, nf = cfg->max_frames;
     if (cfg->grid_kind == BVX_GRID_DENSE) h->table_slots = ncells * nf;
     else h->table_slots = 2 * np + 1024 * nf;
@@ -430,7 +411,6 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
     if (B > h->cfg.max_frames)
         return fail(h, BVX_ERR_WORKSPACE, "%d frames exceed the handle capacity max_frames=%d", B, h->cfg.max_frames);
     h->all_plain = all_plain;
-    h->table_used = tb;
     if (tb > h->table_slots || wd > h->words_cap || ck > h->chunks_cap || (int)h->h_segs.size() > h->seg_cap)
         return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, words %lld/%lld, segs %zu/%d)",
                     tb, h->table_slots, wd, h->words_cap, h->h_segs.size(), h->seg_cap);
@@ -480,21 +460,7 @@ static void launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 bloc
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    int na = 0;
-    if (h->l2_window_max > 0 && h->table_used > 0) {
-        const size_t bytes = std::min((size_t)h->table_used * 8, h->l2_window_max);
-        attr[na].id = cudaLaunchAttributeAccessPolicyWindow;
-        attr[na].val.accessPolicyWindow.base_ptr = h->table;
-        attr[na].val.accessPolicyWindow.num_bytes = bytes;
-        attr[na].val.accessPolicyWindow.hitRatio =
-            bytes <= h->l2_persist ? 1.0f : (float)((double)h->l2_persist / (double)bytes);
-        attr[na].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        attr[na].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        ++na;
-    }
-    cfg.attrs = attr;
-    cfg.numAttrs = na;
+    (void)h;
     cudaLaunchKernelEx(&cfg, kern, args...);
     g_launches += 1;
 }
@@ -550,8 +516,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.frame_base = o.frame_base;
     p.ovf_cap = h->cfg.max_points;
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
-    p.dbg = getenv("BVX_DEBUG_MODE") ? atoi(getenv("BVX_DEBUG_MODE")) : 0;
-    p.bulk_clear = (h->cfg.grid_kind == BVX_GRID_HASHED && !(p.dbg & 1)) ? 1 : 0;
+    p.bulk_clear = h->cfg.grid_kind == BVX_GRID_HASHED ? 1 : 0;
     p.voxels = o.voxels;
     p.coors = o.coors;
     p.num_points = o.num_points;
@@ -566,8 +531,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     (void)max_words;
     if (chunks > 0) {
         ProfScope ps(h, 0, st);
-        const int G = getenv("BVX_INSERT_GROUP") ? std::max(1, std::min(B, atoi(getenv("BVX_INSERT_GROUP")))) : B;
-        launch_k(h, k_insert, dim3(G, chunks, (B + G - 1) / G), kBlock, 0, st, p);
+        launch_k(h, k_insert, dim3(B, chunks), kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);

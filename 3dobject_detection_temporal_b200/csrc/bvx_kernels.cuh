@@ -105,7 +105,6 @@ struct Pipe {
     int frame_base;      // batch index of frame 0 of this call (sub-batches of a pipelined host call)
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
-    int dbg;             // BVX_DEBUG_MODE experiments (0 = product behaviour)
     int bulk_clear;      // hashed tables: cleared by streaming stores in the gather (no per-entry reset)
     // outputs
     float* voxels;
@@ -228,8 +227,7 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 __global__ void __launch_bounds__(kBlock, 8) k_insert(const Pipe p)
 {
     __shared__ int s_chunk;
-    const int f = blockIdx.z * gridDim.x + blockIdx.x;
-    if (f >= p.nframes) return;
+    const int f = blockIdx.x;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.y * kChunk >= fr.n) return;
     FrameState* st = p.state + f;

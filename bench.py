@@ -48,7 +48,6 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not pin the process to the GPU's NUMA node")
-    ap.add_argument("--extra", action="store_true", help="also time cfg1/2/3/5 single calls")
     return ap.parse_args()
 
 

@@ -28,5 +28,5 @@ for i in range(steps):
     gen.generate_batched(sets[i % 3], offs, mean_channels=4, padded=True, out=out)
 torch.cuda.synchronize()
 pr = gen.profile_read()
-print(f"frames={frames_n} {overflow} dbg={os.environ.get('BVX_DEBUG_MODE','0')} step={tot*1e3:.1f}us " +
+print(f"frames={frames_n} {overflow} step={tot*1e3:.1f}us " +
       " ".join(f"{k}={v[0]/v[1]*1e3:.1f}" for k, v in pr.items()))
