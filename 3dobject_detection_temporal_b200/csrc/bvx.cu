@@ -37,6 +37,7 @@ struct bvx_handle {
     unsigned long long* table = nullptr;
     int* slot = nullptr;
     unsigned int* cand = nullptr;
+    unsigned int* lost = nullptr;
     unsigned int* first = nullptr;
     int* wordlocal = nullptr;
     int* chunkbase = nullptr;
@@ -196,7 +197,7 @@ extern "C" int bvx_destroy(bvx_handle* h)
 {
     if (!h) return BVX_OK;
     cudaSetDevice(h->device);
-    cudaFree(h->table); cudaFree(h->slot); cudaFree(h->cand); cudaFree(h->first);
+    cudaFree(h->table); cudaFree(h->slot); cudaFree(h->cand); cudaFree(h->lost); cudaFree(h->first);
     cudaFree(h->wordlocal); cudaFree(h->chunkbase); cudaFree(h->bucket); cudaFree(h->cnt); cudaFree(h->ovf);
     cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
     cudaFree(h->d_offsets_scratch);
@@ -274,6 +275,8 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if ((e = dalloc(h, &h->table, (size_t)h->table_slots)) != cudaSuccess) return bail(e, "alloc table");
     if ((e = dalloc(h, &h->slot, (size_t)np)) != cudaSuccess) return bail(e, "alloc slot");
     if ((e = dalloc(h, &h->cand, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc cand");
+    if ((e = dalloc(h, &h->lost, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc lost");
+    if ((e = cudaMemset(h->lost, 0, (size_t)h->words_cap * 4)) != cudaSuccess) return bail(e, "memset lost");
     if ((e = dalloc(h, &h->first, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc first");
     if ((e = dalloc(h, &h->wordlocal, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc wordlocal");
     h->chunks_cap = np / kChunk + 2 * nf + 8;
@@ -498,6 +501,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.table = h->table;
     p.slot = h->slot;
     p.cand = h->cand;
+    p.lost = h->lost;
     p.first = h->first;
     p.wordlocal = h->wordlocal;
     p.chunkbase = h->chunkbase;
@@ -535,7 +539,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
-        launch_k(h, k_verify, dim3(std::max(chunks, 1), B), kBlock, 0, st, p);
+        launch_k(h, k_verify, dim3((std::max(chunks, 1) + kWarps - 1) / kWarps, B), kBlock, 0, st, p);
     }
     if (chunks > 0) {
         { ProfScope ps(h, 3, st); const int sgx = p.overflow_continue ? chunks : 48;   // measured: break is flat from 32 to 64, continue wants all chunks

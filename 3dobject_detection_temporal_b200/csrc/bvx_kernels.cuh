@@ -85,8 +85,9 @@ struct Pipe {
     const SegDesc* segs;
     FrameState* state;
     unsigned long long* table;
-    int* slot;
+    int* slot;           // per point: index of the first point of its cell as seen when it was inserted (-1: out of range)
     unsigned int* cand;
+    unsigned int* lost;  // per point bit: was the cell's first point for a while, then displaced by an earlier one
     unsigned int* first;
     int* wordlocal;      // exclusive prefix of first-occurrence counts inside the word's chunk
     int* chunkbase;      // per chunk: count, then exclusive prefix over the frame's chunks
@@ -224,7 +225,12 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 //   atomicCAS(empty -> {cell, i}):  was empty   -> new cell, I am a candidate
 //                                   same cell   -> atomicMin if my index is smaller
 //                                   other cell  -> probe the next slot
-__global__ void __launch_bounds__(kBlock, 8) k_insert(const Pipe p)
+// A point whose atomicMin displaces the entry of a later point marks that point in the
+// `lost` bitmap, so after the kernel   first = cand & ~lost   holds exactly the points that
+// are still table entries -- no pass over the table is needed to find them.  Every point
+// also records the first point of its cell as it saw it (slot[]); k_slot trusts that
+// record iff the recorded point is still a first point.
+__global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
 {
     __shared__ int s_chunk;
     const int f = blockIdx.x;
@@ -284,13 +290,22 @@ __global__ void __launch_bounds__(kBlock, 8) k_insert(const Pipe p)
             const unsigned int bit = 1u << k;
             if (!(active & bit)) continue;
             const unsigned int i = (unsigned)(base + k * kBlock + threadIdx.x);
+            // a point that is done keeps, in h[k], the first point of its cell as it saw it
             if (needmin & bit) {
-                if ((unsigned)r[k] > i) wonmask |= bit;
+                const unsigned int o = (unsigned)r[k];
+                if (o > i) {
+                    wonmask |= bit;
+                    atomicOr(p.lost + fr.word_off + (o >> 5), 1u << (o & 31));   // o is no longer first
+                    h[k] = i;
+                } else {
+                    h[k] = o;
+                }
                 active &= ~bit;
             } else if (r[k] == kEmpty64) {
                 wonmask |= bit; ++nnew; active &= ~bit;
+                h[k] = i;
             } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
-                if ((unsigned)r[k] > i) needmin |= bit; else active &= ~bit;
+                if ((unsigned)r[k] > i) needmin |= bit; else { active &= ~bit; h[k] = (unsigned)r[k]; }
             } else {
                 h[k] = (h[k] + 1) & fr.tbl_mask;
             }
@@ -424,59 +439,46 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, i
     }
 }
 
-// grid (max chunks per frame, B); same point mapping as k_insert.
+// grid (ceil(max chunks per frame / 8), B): one warp per chunk, one lane per 32-point word.
+// first = cand & ~lost; per-word and per-chunk counts; the block that finishes a frame's last
+// chunk runs the frame-level scan.  Clears the lost words it read (clean for the next call).
 __global__ void __launch_bounds__(kBlock, 8) k_verify(const Pipe p)
 {
-    __shared__ unsigned int s_first[kChunkWords];
     __shared__ int sm[kWarps + 1];
     __shared__ int s_last;
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
-    const int base = blockIdx.x * kChunk;
     const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));   // prefix that went through k_insert
-    if (base >= eff && !(eff == 0 && blockIdx.x == 0)) return;
+    const int nchunks = (eff + kChunk - 1) / kChunk;
+    const int c0 = blockIdx.x * kWarps;
+    if (c0 >= nchunks && !(eff == 0 && blockIdx.x == 0)) return;
     const int nwords = (eff + 31) / 32;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const unsigned long long* tbl = p.table + fr.tbl_off;
-    if (eff > 0) {
-        int sl[kPts];
-        bool cd[kPts];
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) {
-            const int i = base + k * kBlock + threadIdx.x;
-            const int w = i >> 5;
-            const unsigned int cw = w < nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
-            cd[k] = (cw >> lane) & 1u;
-            sl[k] = cd[k] ? __ldg(p.slot + fr.pt_off + i) : 0;
+    const int c = c0 + wid;
+    if (c < nchunks) {
+        const int w = c * kChunkWords + lane;
+        unsigned int fw = 0;
+        if (w < nwords) {
+            const unsigned int lw = __ldcg(p.lost + fr.word_off + w);
+            fw = __ldcg(p.cand + fr.word_off + w) & ~lw;
+            if (lw) p.lost[fr.word_off + w] = 0u;
+            // points past the inserted prefix carry no bits: cand words are written whole by k_insert
         }
-        unsigned long long e[kPts];
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) e[k] = cd[k] ? __ldcg(tbl + sl[k]) : 0ull;
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) {
-            const int i = base + k * kBlock + threadIdx.x;
-            const bool isf = cd[k] && (unsigned)e[k] == (unsigned)i;
-            const unsigned int b = __ballot_sync(0xffffffffu, isf);
-            if (lane == 0) s_first[k * kWarps + wid] = b;
+        int tot;
+        const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
+        if (w < nwords) {
+            p.first[fr.word_off + w] = fw;
+            p.wordlocal[fr.word_off + w] = ex;
         }
-        __syncthreads();
-        if (wid == 0) {
-            const unsigned int fw = s_first[lane];
-            int tot;
-            const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
-            const int w = blockIdx.x * kChunkWords + lane;
-            if (w < nwords) {
-                p.first[fr.word_off + w] = fw;
-                p.wordlocal[fr.word_off + w] = ex;
-            }
-            if (lane == 0) p.chunkbase[fr.chunk_off + blockIdx.x] = tot;
-        }
+        if (lane == 0) p.chunkbase[fr.chunk_off + c] = tot;
     }
     // last chunk of the frame -> frame-level scan
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0)
-        s_last = (atomicAdd(&p.state[f].done_verify, 1) == max((eff + kChunk - 1) / kChunk, 1) - 1);
+    if (threadIdx.x == 0) {
+        const int mine = eff == 0 ? 1 : min(kWarps, nchunks - c0);
+        s_last = (atomicAdd(&p.state[f].done_verify, mine) + mine == max(nchunks, 1));
+    }
     __syncthreads();
     if (!s_last) return;
     __threadfence();
@@ -484,10 +486,27 @@ __global__ void __launch_bounds__(kBlock, 8) k_verify(const Pipe p)
 }
 
 // ---------------------------------------------------------------- k_slot
+// Rare path of k_slot: the first point a point recorded at insert time was displaced later
+// (chunks of one cell finishing out of order): find the cell's entry in the table.
+__device__ __forceinline__ unsigned int refind_first(const Pipe& p, const FrameDesc& fr, int i)
+{
+    float x, y, z;
+    load_xyz(p, fr, i, x, y, z);
+    const unsigned int cell = (unsigned)cell_of(p.g, x, y, z);
+    const unsigned long long* tbl = p.table + fr.tbl_off;
+    unsigned int hh = fr.tbl_shift < 0 ? cell : hash_cell(cell, fr.tbl_shift);
+    unsigned long long e = __ldcg(tbl + hh);
+    while ((unsigned)(e >> 32) != cell) {
+        hh = (hh + 1) & fr.tbl_mask;
+        e = __ldcg(tbl + hh);
+    }
+    return (unsigned)e;
+}
+
 // grid (gx, B): block x of frame f walks chunks x, x+gx, ... below the break
 // cut-off, so the launch carries no blocks that only exit.  Same round structure as
 // k_insert: per round one atomic per point in flight.
-__global__ void __launch_bounds__(kBlock) k_slot(const Pipe p)
+__global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
 {
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
@@ -496,33 +515,35 @@ __global__ void __launch_bounds__(kBlock) k_slot(const Pipe p)
         p.state[f].ticket = 0ull;
         p.state[f].n_eff = 0x7FFFFFFF;
     }
-    const unsigned long long* tbl = p.table + fr.tbl_off;
     const int T = p.T;
     for (int base = blockIdx.x * kChunk; base < lim; base += gridDim.x * kChunk) {
         int sl[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             const int i = base + k * kBlock + threadIdx.x;
-            sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;
+            sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;   // first point of my cell, as seen at insert
         }
-        unsigned long long e[kPts];
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) e[k] = sl[k] >= 0 ? __ldcg(tbl + sl[k]) : 0ull;
         int rank[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             rank[k] = 0x7FFFFFFF;
             if (sl[k] >= 0) {
-                const unsigned int fidx = (unsigned)e[k];
+                unsigned int fidx = (unsigned)sl[k];
+                unsigned int fw = __ldg(p.first + fr.word_off + (fidx >> 5));
+                if (!((fw >> (fidx & 31)) & 1u)) {
+                    fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
+                    fw = __ldg(p.first + fr.word_off + (fidx >> 5));
+                }
                 const int w = fidx >> 5;
                 rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
-                          __ldg(p.wordlocal + fr.word_off + w) +
-                          __popc(__ldg(p.first + fr.word_off + w) & ((1u << (fidx & 31)) - 1u));
+                          __ldg(p.wordlocal + fr.word_off + w) + __popc(fw & ((1u << (fidx & 31)) - 1u));
             }
         }
         // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
         if (T <= kChainMaxT) {
-            // sorted insertion: slot j ends up holding the (j+1)-th smallest index offered
+            // sorted insertion: slot j ends up holding the (j+1)-th smallest index offered.
+            // (A plain store of the first point into slot 0 instead of its atomic was measured:
+            // k_slot -4 us, but the gather then pays the bucket's DRAM fill, +7 us.)
             int cur[kPts];
             int* b[kPts];
             unsigned int active = 0;
@@ -584,9 +605,9 @@ __global__ void __launch_bounds__(kBlock) k_overflow(const Pipe p)
 }
 
 // ---------------------------------------------------------------- k_gather
-// Table reset, shared by both gather kernels: blocks past the voxel tiles walk the
-// frame's chunks and clear the slot of every candidate (a superset of the entries
-// the frame created), so the next call starts from an empty table without a memset.
+// Dense-grid table reset, shared by both gather kernels: blocks past the voxel tiles walk
+// the frame's chunks and clear the cell of every candidate (a superset of the entries the
+// frame created), so the next call starts from an empty grid without a memset.
 __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, int chunk)
 {
     const int base = chunk * kChunk;
@@ -600,7 +621,11 @@ __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, 
         const int i = base + k * kBlock + threadIdx.x;
         const int w = i >> 5;
         const unsigned int cw = w < nwords ? __ldg(p.cand + fr.word_off + w) : 0u;
-        if ((cw >> lane) & 1u) tbl[__ldg(p.slot + fr.pt_off + i)] = kEmpty64;
+        if ((cw >> lane) & 1u) {
+            float x, y, z;
+            load_xyz(p, fr, i, x, y, z);
+            tbl[cell_of(p.g, x, y, z)] = kEmpty64;      // dense grid: slot = cell
+        }
     }
 }
 
