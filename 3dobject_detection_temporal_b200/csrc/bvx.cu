@@ -520,7 +520,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.frame_base = o.frame_base;
     p.ovf_cap = h->cfg.max_points;
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
-    p.bulk_clear = h->cfg.grid_kind == BVX_GRID_HASHED ? 1 : 0;
+    p.clear_rows = 0;
     p.voxels = o.voxels;
     p.coors = o.coors;
     p.num_points = o.num_points;
@@ -529,13 +529,20 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
 
     const int T = p.T;
     const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
-    const int rchunks = p.bulk_clear ? 0 : chunks;      // per-entry reset blocks (dense grid only)
-    if (chunks > 65535 || B > 65535)
+    const bool hashed = h->cfg.grid_kind == BVX_GRID_HASHED;
+    const int rchunks = hashed ? 0 : chunks;            // per-entry reset blocks (dense grid only)
+    if (hashed && chunks > 0) {
+        // one clear row per 64 KB of the largest frame's table (measured: 16 KB .. 256 KB slices are
+        // within 2 % of each other at 64 frames; small slices keep the single-frame latency down)
+        const unsigned long long tbytes = (1ull << ilog2_ceil((unsigned long long)max_n + 1)) * 8;
+        p.clear_rows = (int)std::max<unsigned long long>(1, std::min<unsigned long long>(256, tbytes / (64 * 1024)));
+    }
+    if (chunks > 65535 - 256 || B > 65535)
         return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call and 67M points per frame");
     (void)max_words;
     if (chunks > 0) {
         ProfScope ps(h, 0, st);
-        launch_k(h, k_insert, dim3(B, chunks), kBlock, 0, st, p);
+        launch_k(h, k_insert, dim3(B, p.clear_rows + chunks), kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);

@@ -77,6 +77,8 @@ struct FrameState {
                                 // order), high 32 bits = cells claimed so far -- one atomic returns both
     int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
     int n_done;       // points that went through k_insert (prefix), published by the scan
+    int cleared;      // k_insert: table slices cleared so far (hashed grid); reset by k_slot
+    int pad_;
 };
 
 struct Pipe {
@@ -106,7 +108,7 @@ struct Pipe {
     int frame_base;      // batch index of frame 0 of this call (sub-batches of a pipelined host call)
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
-    int bulk_clear;      // hashed tables: cleared by streaming stores in the gather (no per-entry reset)
+    int clear_rows;      // hashed tables: the first clear_rows block rows of k_insert clear the tables (0: dense grid)
     // outputs
     float* voxels;
     int* coors;
@@ -205,8 +207,8 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 }
 
 // ---------------------------------------------------------------- k_insert
-// grid (B, max chunks per frame): x = frame, so blocks are dispatched chunk-row by
-// chunk-row across all frames.  A block takes the frame's next chunk in index order
+// grid (B, clear rows + max chunks per frame): x = frame, so blocks are dispatched row by
+// row across all frames: first the rows that clear the tables, then the chunk rows.  A block takes the frame's next chunk in index order
 // from a ticket counter.  Thread t of chunk c owns points c*1024 + k*256 + t,
 // k = 0..3: every warp-wide access is coalesced and a warp covers exactly one
 // 32-point mask word per k.
@@ -235,10 +237,32 @@ __global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
     __shared__ int s_chunk;
     const int f = blockIdx.x;
     const FrameDesc fr = p.frames[f];
-    if ((int)blockIdx.y * kChunk >= fr.n) return;
     FrameState* st = p.state + f;
+    if ((int)blockIdx.y < p.clear_rows) {
+        // Clear rows: the frame's table is emptied here, right before it is used, with normal
+        // stores -- whole sectors, so the lines are allocated in the L2 without a DRAM fill and
+        // the atomics below find them there.  These blocks never wait, so the insert blocks of
+        // the frame (later in dispatch order) can safely wait for them.
+        if (fr.n > 0) {
+            const unsigned int n2 = (fr.tbl_mask + 1u) >> 1;        // uint4 = two slots
+            const unsigned int per = (n2 + p.clear_rows - 1) / p.clear_rows;
+            const unsigned int lo = blockIdx.y * per, hi = min(n2, lo + per);
+            uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
+            const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+            for (unsigned int j = lo + threadIdx.x; j < hi; j += kBlock) t4[j] = e;
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) atomicAdd(&st->cleared, 1);
+        }
+        return;
+    }
+    if ((int)(blockIdx.y - p.clear_rows) * kChunk >= fr.n) return;
     const bool brk = !p.overflow_continue;
     if (threadIdx.x == 0) {
+        if (p.clear_rows) {
+            while (*(volatile int*)&st->cleared < p.clear_rows) { }
+            __threadfence();
+        }
         const unsigned long long t = atomicAdd(&st->ticket, 1ull);
         int c = (int)(unsigned int)t;
         if (brk && (int)(t >> 32) > p.cap && c * kChunk < fr.n) {
@@ -513,6 +537,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
     const int lim = min(p.state[f].n_done, p.state[f].istar);
     if (blockIdx.x == 0 && threadIdx.x == 0) {   // k_insert's per-frame counters, for the next call
         p.state[f].ticket = 0ull;
+        p.state[f].cleared = 0;
         p.state[f].n_eff = 0x7FFFFFFF;
     }
     const int T = p.T;
@@ -523,21 +548,32 @@ __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
             const int i = base + k * kBlock + threadIdx.x;
             sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;   // first point of my cell, as seen at insert
         }
+        // voxel number = rank of the recorded first point among the frame's first points: three
+        // small lookups, issued together for all four points
+        unsigned int fw[kPts];
         int rank[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
-            rank[k] = 0x7FFFFFFF;
+            fw[k] = 0u;
+            rank[k] = 0;
             if (sl[k] >= 0) {
-                unsigned int fidx = (unsigned)sl[k];
-                unsigned int fw = __ldg(p.first + fr.word_off + (fidx >> 5));
-                if (!((fw >> (fidx & 31)) & 1u)) {
-                    fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
-                    fw = __ldg(p.first + fr.word_off + (fidx >> 5));
-                }
-                const int w = fidx >> 5;
+                const unsigned int fidx = (unsigned)sl[k];
+                fw[k] = __ldg(p.first + fr.word_off + (fidx >> 5));
                 rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
-                          __ldg(p.wordlocal + fr.word_off + w) + __popc(fw & ((1u << (fidx & 31)) - 1u));
+                          __ldg(p.wordlocal + fr.word_off + (fidx >> 5));
             }
+        }
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            if (sl[k] < 0) { rank[k] = 0x7FFFFFFF; continue; }
+            unsigned int fidx = (unsigned)sl[k];
+            if (!((fw[k] >> (fidx & 31)) & 1u)) {
+                fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
+                fw[k] = __ldg(p.first + fr.word_off + (fidx >> 5));
+                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
+                          __ldg(p.wordlocal + fr.word_off + (fidx >> 5));
+            }
+            rank[k] += __popc(fw[k] & ((1u << (fidx & 31)) - 1u));
         }
         // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
         if (T <= kChainMaxT) {
@@ -629,19 +665,6 @@ __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, 
     }
 }
 
-// Hashed tables are small (the next power of two above the frame's point count, 8 bytes per
-// slot): every gather block clears its slice of the frame's table with streaming 16-byte
-// stores -- sequential DRAM traffic instead of one random read-modify-write per entry.
-__device__ __forceinline__ void clear_table_slice(const Pipe& p, const FrameDesc& fr, int tiles)
-{
-    const unsigned int n2 = (fr.tbl_mask + 1u) >> 1;            // uint4 = two slots
-    const unsigned int per = (n2 + tiles - 1) / tiles;
-    const unsigned int lo = blockIdx.x * per, hi = min(n2, lo + per);
-    uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
-    const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-    for (unsigned int j = lo + threadIdx.x; j < hi; j += kBlock) __stcs(t4 + j, e);
-}
-
 __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int cell)
 {
     const int gx = p.g.gs[0], gy = p.g.gs[1];
@@ -667,7 +690,6 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
-    if (p.bulk_clear) clear_table_slice(p, fr, tiles);
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * kBlock;
     if (v0 >= mf) return;
@@ -742,7 +764,6 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
-    if (p.bulk_clear) clear_table_slice(p, fr, tiles);
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * vt;
     if (v0 >= mf) return;
