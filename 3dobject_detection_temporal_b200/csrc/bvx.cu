@@ -290,18 +290,10 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if ((e = dalloc(h, &h->d_segs, (size_t)h->seg_cap)) != cudaSuccess) return bail(e, "alloc segs");
     if ((e = dalloc(h, &h->d_state, (size_t)nf)) != cudaSuccess) return bail(e, "alloc state");
     if ((e = dalloc(h, &h->d_offsets_scratch, (size_t)nf + 1)) != cudaSuccess) return bail(e, "alloc offsets");
-    // one-time initialisation; every call leaves the workspace clean again
-    if ((e = cudaMemset(h->table, 0xFF, (size_t)h->table_slots * 8)) != cudaSuccess) return bail(e, "memset table");
-    {
-        const size_t nb = (size_t)h->voxel_cap * cfg->max_num_points;
-        std::vector<int> fillv(std::min<size_t>(nb, 1 << 20), kEmptyIdx);
-        for (size_t off = 0; off < nb; off += fillv.size()) {
-            const size_t c = std::min(fillv.size(), nb - off);
-            if ((e = cudaMemcpy(h->bucket + off, fillv.data(), c * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
-                return bail(e, "init bucket");
-        }
-    }
-    if ((e = cudaMemset(h->cnt, 0, (size_t)h->voxel_cap * 4)) != cudaSuccess) return bail(e, "memset cnt");
+    // one-time initialisation of what a call expects clean (hashed tables, bucket rows and voxel
+    // counters are emptied by the call itself right before use)
+    if (cfg->grid_kind == BVX_GRID_DENSE)
+        if ((e = cudaMemset(h->table, 0xFF, (size_t)h->table_slots * 8)) != cudaSuccess) return bail(e, "memset table");
     if ((e = cudaMemset(h->counters, 0, 32)) != cudaSuccess) return bail(e, "memset counters");
     {
         FrameState z;
@@ -546,7 +538,11 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
-        launch_k(h, k_verify, dim3((std::max(chunks, 1) + kWarps - 1) / kWarps, B), kBlock, 0, st, p);
+        // one warp per chunk, and enough blocks that none clears more than 8192 bucket entries
+        const long long clr = (long long)std::min(cap, max_n) * (T <= kChainMaxT ? T : 1);
+        const int vgx = (int)std::min<long long>(65535, std::max<long long>((std::max(chunks, 1) + kWarps - 1) / kWarps,
+                                                                            (clr + 8191) / 8192));
+        launch_k(h, k_verify, dim3(vgx, B), kBlock, 0, st, p);
     }
     if (chunks > 0) {
         { ProfScope ps(h, 3, st); const int sgx = p.overflow_continue ? chunks : 48;   // measured: break is flat from 32 to 64, continue wants all chunks

@@ -475,6 +475,19 @@ __global__ void __launch_bounds__(kBlock, 8) k_verify(const Pipe p)
     const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));   // prefix that went through k_insert
     const int nchunks = (eff + kChunk - 1) / kChunk;
     const int c0 = blockIdx.x * kWarps;
+    {
+        // Every block of the frame also empties its share of the frame's bucket rows (T <= 8:
+        // the sorted chain needs them empty) or voxel counters (larger T), right before k_slot
+        // fills them: whole sectors, normal stores, so k_slot's atomics find the lines in the L2.
+        const bool chain = p.T <= kChainMaxT;
+        int* base = chain ? p.bucket + (size_t)f * p.cap * p.T : p.cnt + (size_t)f * p.cap;
+        const int rows = min(p.cap, fr.n);                  // a frame of n points opens at most n voxels
+        const int total = chain ? rows * p.T : rows;
+        const int per = (total + gridDim.x - 1) / gridDim.x;
+        const int lo = blockIdx.x * per, hi = min(total, lo + per);
+        const int fill = chain ? kEmptyIdx : 0;
+        for (int j = lo + threadIdx.x; j < hi; j += kBlock) base[j] = fill;
+    }
     if (c0 >= nchunks && !(eff == 0 && blockIdx.x == 0)) return;
     const int nwords = (eff + 31) / 32;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -702,7 +715,6 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
 #pragma unroll
     for (int s = 0; s < T; ++s) {
         idx[s] = live ? gb[s] : kEmptyIdx;
-        if (live) gb[s] = kEmptyIdx;
     }
     float4 row[T];
     int nvalid = 0;
@@ -774,18 +786,13 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
     int* scnt = smem_i + ((vt * T + 3) & ~3);                  // live entries per voxel
     float* srow = reinterpret_cast<float*>(scnt + ((vt + 3) & ~3));
     int* gb = p.bucket + ((size_t)f * p.cap + v0) * T;
-    for (int e = threadIdx.x; e < E; e += kBlock) {
-        sidx[e] = gb[e];
-        gb[e] = kEmptyIdx;
-    }
+    for (int e = threadIdx.x; e < E; e += kBlock) sidx[e] = gb[e];
     if (T > kChainMaxT) {
         // count + bucket path: the counter says how many points the voxel saw; the live
         // entries are the first min(count, T) positions of its bucket, in arrival order
-        for (int v = threadIdx.x; v < nv; v += kBlock) {
-            int* c = p.cnt + (size_t)f * p.cap + v0 + v;
-            scnt[v] = min(*c, T);
-            *c = 0;
-        }
+        // (what lies behind them is left over from earlier calls)
+        for (int v = threadIdx.x; v < nv; v += kBlock)
+            scnt[v] = min(p.cnt[(size_t)f * p.cap + v0 + v], T);
         __syncthreads();
     } else {
         __syncthreads();
@@ -801,7 +808,7 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
         const int v = e / T, s = e - v * T;
         const int my = sidx[e];
         const int nvalid = scnt[v];
-        if (my != kEmptyIdx) {
+        if (s < nvalid) {               // (T <= 8: the chain fills slots 0 .. nvalid-1 in order)
             const int* vb = sidx + v * T;
             int r = 0;
             for (int k = 0; k < nvalid; ++k) r += (vb[k] < my);   // slot = rank of the index in the voxel
