@@ -582,6 +582,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
             unsigned int fidx = (unsigned)sl[k];
             if (!((fw[k] >> (fidx & 31)) & 1u)) {
                 fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
+                sl[k] = (int)fidx;
                 fw[k] = __ldg(p.first + fr.word_off + (fidx >> 5));
                 rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
                           __ldg(p.wordlocal + fr.word_off + (fidx >> 5));
@@ -590,9 +591,9 @@ __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
         }
         // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
         if (T <= kChainMaxT) {
-            // sorted insertion: slot j ends up holding the (j+1)-th smallest index offered.
-            // (A plain store of the first point into slot 0 instead of its atomic was measured:
-            // k_slot -4 us, but the gather then pays the bucket's DRAM fill, +7 us.)
+            // Slot 0 belongs to the voxel's first point (the smallest index by definition): a plain
+            // store into the row k_verify just emptied, no round trip.  The other points go through a
+            // sorted insertion over slots 1 .. T-1: slot j ends up holding the (j+1)-th smallest index.
             int cur[kPts];
             int* b[kPts];
             unsigned int active = 0;
@@ -600,9 +601,12 @@ __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
             for (int k = 0; k < kPts; ++k) {
                 cur[k] = base + k * kBlock + threadIdx.x;
                 b[k] = p.bucket + ((size_t)f * p.cap + (rank[k] < p.cap ? rank[k] : 0)) * T;
-                if (rank[k] < p.cap) active |= 1u << k;
+                if (rank[k] < p.cap) {
+                    if (sl[k] == cur[k]) b[k][0] = cur[k];
+                    else active |= 1u << k;
+                }
             }
-            for (int j = 0; j < T && active; ++j) {
+            for (int j = 1; j < T && active; ++j) {
                 int old[kPts];
 #pragma unroll
                 for (int k = 0; k < kPts; ++k)
