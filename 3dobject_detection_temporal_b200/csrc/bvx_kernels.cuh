@@ -259,10 +259,6 @@ __global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
     if ((int)(blockIdx.y - p.clear_rows) * kChunk >= fr.n) return;
     const bool brk = !p.overflow_continue;
     if (threadIdx.x == 0) {
-        if (p.clear_rows) {
-            while (*(volatile int*)&st->cleared < p.clear_rows) { }
-            __threadfence();
-        }
         const unsigned long long t = atomicAdd(&st->ticket, 1ull);
         int c = (int)(unsigned int)t;
         if (brk && (int)(t >> 32) > p.cap && c * kChunk < fr.n) {
@@ -290,6 +286,14 @@ __global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
     }
     unsigned int active = 0, needmin = 0, wonmask = 0;
     int nnew = 0;
+    if (p.clear_rows) {
+        // the table must be empty before the first atomic (the point loads above did not need it)
+        if (threadIdx.x == 0) {
+            while (*(volatile int*)&st->cleared < p.clear_rows) { }
+            __threadfence();
+        }
+        __syncthreads();
+    }
 #pragma unroll
     for (int k = 0; k < kPts; ++k) {
         h[k] = 0;
