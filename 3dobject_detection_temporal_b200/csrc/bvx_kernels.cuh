@@ -566,32 +566,35 @@ __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
             sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;   // first point of my cell, as seen at insert
         }
         // voxel number = rank of the recorded first point among the frame's first points: three
-        // small lookups, issued together for all four points
+        // small lookups, issued unconditionally (index 0 for out-of-range points) for all four points
         unsigned int fw[kPts];
         int rank[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
-            fw[k] = 0u;
-            rank[k] = 0;
-            if (sl[k] >= 0) {
-                const unsigned int fidx = (unsigned)sl[k];
-                fw[k] = __ldg(p.first + fr.word_off + (fidx >> 5));
-                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
-                          __ldg(p.wordlocal + fr.word_off + (fidx >> 5));
-            }
+            const unsigned int fidx = (unsigned)max(sl[k], 0);
+            const int w = fr.word_off + (int)(fidx >> 5);
+            fw[k] = __ldg(p.first + w);
+            rank[k] = __ldg(p.chunkbase + fr.chunk_off + (int)(fidx / kChunk)) + __ldg(p.wordlocal + w);
         }
+        unsigned int stale = 0;
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
-            if (sl[k] < 0) { rank[k] = 0x7FFFFFFF; continue; }
-            unsigned int fidx = (unsigned)sl[k];
-            if (!((fw[k] >> (fidx & 31)) & 1u)) {
-                fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
+            const unsigned int fidx = (unsigned)max(sl[k], 0);
+            const unsigned int bit = (fw[k] >> (fidx & 31)) & 1u;
+            if (sl[k] >= 0 && !bit) stale |= 1u << k;
+            rank[k] = sl[k] >= 0 ? rank[k] + __popc(fw[k] & ((1u << (fidx & 31)) - 1u)) : 0x7FFFFFFF;
+        }
+        if (stale) {
+            // rare: the recorded point lost its place later; look the cell up in the table
+#pragma unroll
+            for (int k = 0; k < kPts; ++k) {
+                if (!(stale & (1u << k))) continue;
+                const unsigned int fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
                 sl[k] = (int)fidx;
-                fw[k] = __ldg(p.first + fr.word_off + (fidx >> 5));
-                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (fidx / kChunk)) +
-                          __ldg(p.wordlocal + fr.word_off + (fidx >> 5));
+                const int w = fr.word_off + (int)(fidx >> 5);
+                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (int)(fidx / kChunk)) + __ldg(p.wordlocal + w) +
+                          __popc(__ldg(p.first + w) & ((1u << (fidx & 31)) - 1u));
             }
-            rank[k] += __popc(fw[k] & ((1u << (fidx & 31)) - 1u));
         }
         // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
         if (T <= kChainMaxT) {
