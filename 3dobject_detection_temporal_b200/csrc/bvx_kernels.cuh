@@ -73,8 +73,9 @@ struct FrameState {
     int m;            // voxels kept = min(total, cap)
     int istar;        // break cut-off: points with index >= istar are dropped
     int done_verify;  // chunks of k_verify finished (last-block detection); reset by the scanner
-    unsigned long long ticket;  // k_insert: low 32 bits = next chunk of the frame to hand out (in index
-                                // order), high 32 bits = cells claimed so far -- one atomic returns both
+    unsigned long long ticket;  // k_insert: bits 0-30 = next chunk of the frame to hand out (in index order),
+                                // bit 31 = table known to be empty, high 32 bits = cells claimed so far --
+                                // one atomic returns all three
     int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
     int n_done;       // points that went through k_insert (prefix), published by the scan
     int cleared;      // k_insert: table slices cleared so far (hashed grid); reset by k_slot
@@ -234,7 +235,7 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // record iff the recorded point is still a first point.
 __global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
 {
-    __shared__ int s_chunk;
+    __shared__ int s_chunk, s_ready;
     const int f = blockIdx.x;
     const FrameDesc fr = p.frames[f];
     FrameState* st = p.state + f;
@@ -260,7 +261,8 @@ __global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
     const bool brk = !p.overflow_continue;
     if (threadIdx.x == 0) {
         const unsigned long long t = atomicAdd(&st->ticket, 1ull);
-        int c = (int)(unsigned int)t;
+        int c = (int)((unsigned int)t & 0x7FFFFFFFu);
+        s_ready = (int)(((unsigned int)t >> 31) | (p.clear_rows == 0));   // bit 31: the table is known to be empty
         if (brk && (int)(t >> 32) > p.cap && c * kChunk < fr.n) {
             atomicMin(&st->n_eff, c * kChunk);
             c = 0x7FFFFFF;                             // skipped
@@ -286,11 +288,16 @@ __global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
     }
     unsigned int active = 0, needmin = 0, wonmask = 0;
     int nnew = 0;
-    if (p.clear_rows) {
-        // the table must be empty before the first atomic (the point loads above did not need it)
+    if (!s_ready) {
+        // The table must be empty before the first atomic (the point loads above did not need it).
+        // The first block of a frame to see all clear rows done says so in bit 31 of the ticket
+        // word; blocks that get the bit with their ticket skip this wait and its barrier.  (The clear
+        // stores were fenced to the L2 before `cleared` was bumped, and the table is only ever
+        // touched by atomics, which act at the L2.)
         if (threadIdx.x == 0) {
             while (*(volatile int*)&st->cleared < p.clear_rows) { }
             __threadfence();
+            atomicOr(&st->ticket, 0x80000000ull);
         }
         __syncthreads();
     }
