@@ -233,7 +233,7 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // are still table entries -- no pass over the table is needed to find them.  Every point
 // also records the first point of its cell as it saw it (slot[]); k_slot trusts that
 // record iff the recorded point is still a first point.
-__global__ void __launch_bounds__(kBlock, 6) k_insert(const Pipe p)
+__global__ void __launch_bounds__(kBlock, 8) k_insert(const Pipe p)
 {
     __shared__ int s_chunk, s_ready;
     const int f = blockIdx.x;
