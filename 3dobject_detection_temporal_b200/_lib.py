@@ -48,6 +48,14 @@ class BvxSweep(ctypes.Structure):
     ]
 
 
+class BvxCrop(ctypes.Structure):
+    _fields_ = [
+        ("n_planes", ctypes.c_int32),
+        ("reserved", ctypes.c_int32),
+        ("planes", (ctypes.c_double * 4) * 8),
+    ]
+
+
 _vp = ctypes.c_void_p
 _i32 = ctypes.c_int32
 
@@ -64,7 +72,8 @@ SYMBOLS = {
     "bvx_generate_batched": (ctypes.c_int, [_vp, _vp, ctypes.POINTER(_i32), _i32, _i32, _i32, _vp, _vp, _vp,
                                             _vp, _vp, _i32, _vp]),
     "bvx_generate_batched_sweeps": (ctypes.c_int, [_vp, ctypes.POINTER(BvxSweep), ctypes.POINTER(_i32), _i32, _i32,
-                                                   _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp]),
+                                                   _i32, ctypes.POINTER(BvxCrop), _i32, _vp, _vp, _vp, _vp, _vp,
+                                                   _i32, _vp]),
     "bvx_generate_host": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, ctypes.POINTER(_i32),
                                          _vp]),
     "bvx_generate_batched_host": (ctypes.c_int, [_vp, _vp, ctypes.POINTER(_i32), _i32, _i32, _i32, _vp, _vp,

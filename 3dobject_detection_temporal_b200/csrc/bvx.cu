@@ -327,6 +327,7 @@ struct FrameSpec {
     const bvx_sweep* sweeps;  // k sweeps (host structs, device point pointers)
     int k;
     int with_dt;
+    const bvx_crop* crop = nullptr;   // optional convex crop on the raw coordinates
 };
 
 static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
@@ -358,6 +359,12 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
             memcpy(sd.R, sw.R, sizeof sd.R);
             memcpy(sd.t, sw.t, sizeof sd.t);
             sd.dt = sw.dt;
+            if (frames[f].crop && frames[f].crop->n_planes > 0) {
+                if (frames[f].crop->n_planes > 8)
+                    return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d: at most 8 crop planes", f);
+                sd.n_planes = frames[f].crop->n_planes;
+                memcpy(sd.planes, frames[f].crop->planes, sizeof(double) * 4 * sd.n_planes);
+            }
             if (((uintptr_t)sw.points & 15) != 0) *all_aligned = false;
             h->h_segs.push_back(sd);
             n += sw.n;
@@ -371,7 +378,8 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
         if (n > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
         fd.n = (int)n;
         fd.pts0 = nullptr;
-        if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform)
+        if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform &&
+            !(frames[f].crop && frames[f].crop->n_planes > 0))
             fd.pts0 = frames[f].sweeps[0].points;
         else if (n > 0)
             all_plain = false;
@@ -534,7 +542,10 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     (void)max_words;
     if (chunks > 0) {
         ProfScope ps(h, 0, st);
-        launch_k(h, k_insert, dim3(B, p.clear_rows + chunks), kBlock, 0, st, p);
+        bool crop = false;
+        for (const FrameSpec& fs : frames) crop |= fs.crop && fs.crop->n_planes > 0;
+        if (crop) launch_k(h, k_insert<true>, dim3(B, p.clear_rows + chunks), kBlock, 0, st, p);
+        else launch_k(h, k_insert<false>, dim3(B, p.clear_rows + chunks), kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
@@ -641,7 +652,8 @@ extern "C" int bvx_generate_batched(bvx_handle* h, const float* points, const in
 }
 
 extern "C" int bvx_generate_batched_sweeps(bvx_handle* h, const bvx_sweep* sweeps, const int32_t* sweep_offsets,
-                                           int32_t b, int32_t f_in, int32_t append_dt, int32_t max_voxels,
+                                           int32_t b, int32_t f_in, int32_t append_dt, const bvx_crop* crops,
+                                           int32_t max_voxels,
                                            float* voxels, int32_t* coors4, int32_t* num_points,
                                            int32_t* frame_voxel_offsets, float* mean, int32_t mean_c, void* stream)
 {
@@ -653,7 +665,7 @@ extern "C" int bvx_generate_batched_sweeps(bvx_handle* h, const bvx_sweep* sweep
     for (int i = 0; i < b; ++i) {
         const int k = sweep_offsets[i + 1] - sweep_offsets[i];
         if (k < 1) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d has no sweep", i);
-        fr[i] = FrameSpec{sweeps + sweep_offsets[i], k, append_dt ? 1 : 0};
+        fr[i] = FrameSpec{sweeps + sweep_offsets[i], k, append_dt ? 1 : 0, crops ? crops + i : nullptr};
     }
     Outputs o{voxels, coors4, num_points, frame_voxel_offsets, nullptr, mean, mean_c, 4, 0};
     return run_pipeline(h, fr, f_in, f_in + (append_dt ? 1 : 0), max_voxels, o, (cudaStream_t)stream);

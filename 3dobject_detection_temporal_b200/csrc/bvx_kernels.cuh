@@ -66,6 +66,8 @@ struct SegDesc {
     float R[9];
     float t[3];
     float dt;
+    int n_planes;       // crop: a point with a*x + b*y + c*z + d >= 0 for any plane is dropped
+    double planes[8][4];
 };
 
 struct FrameState {
@@ -155,7 +157,25 @@ __device__ __forceinline__ unsigned int hash_cell(unsigned int cell, int shift)
     return (cell * 0x9E3779B1u) >> shift;
 }
 
-// xyz of frame-local point i (sweep transform applied)
+// Convex crop on the raw coordinates, the reference's _points_in_convex_polygon_3d_jit
+// (second/core/geometry.py:122-141): float64, sign = x*a + y*b + z*c + d summed left to right,
+// outside iff sign >= 0 for some surface.
+__device__ __forceinline__ bool cropped_out(const SegDesc& sg, float x, float y, float z)
+{
+    bool out = false;
+    for (int k = 0; k < sg.n_planes; ++k) {
+        const double s = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)x, sg.planes[k][0]),
+                                                       __dmul_rn((double)y, sg.planes[k][1])),
+                                             __dmul_rn((double)z, sg.planes[k][2])),
+                                   sg.planes[k][3]);
+        out |= s >= 0.0;
+    }
+    return out;
+}
+
+// xyz of frame-local point i (sweep transform applied).  CROP: also apply the frame's crop planes
+// (only k_insert needs that: every later kernel only looks at points that got a cell).
+template <bool CROP = false>
 __device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int i, float& x, float& y,
                                          float& z)
 {
@@ -177,6 +197,7 @@ __device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int
     } else {
         x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
     }
+    if (CROP && sg.n_planes && cropped_out(sg, x, y, z)) { x = __int_as_float(0x7FC00000); return; }  // NaN: no cell
     xform(sg, x, y, z);
 }
 
@@ -233,7 +254,8 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // are still table entries -- no pass over the table is needed to find them.  Every point
 // also records the first point of its cell as it saw it (slot[]); k_slot trusts that
 // record iff the recorded point is still a first point.
-__global__ void __launch_bounds__(kBlock, 8) k_insert(const Pipe p)
+template <bool CROP>
+__global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
 {
     __shared__ int s_chunk, s_ready;
     const int f = blockIdx.x;
@@ -282,7 +304,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_insert(const Pipe p)
         cell[k] = -1;
         if (i < fr.n) {
             float x, y, z;
-            load_xyz(p, fr, i, x, y, z);
+            load_xyz<CROP>(p, fr, i, x, y, z);
             cell[k] = cell_of(p.g, x, y, z);
         }
     }

@@ -282,11 +282,15 @@ class VoxelGenerator:
             total += int(p.shape[0])
         return f_in, total
 
-    def generate_batched_sweeps(self, frames, max_voxels=None, append_dt=True, mean_channels=0):
+    def generate_batched_sweeps(self, frames, max_voxels=None, append_dt=True, mean_channels=0, crops=None):
         """B frames, each a list of sweeps ``(points[N_s, F_in], R or None, t or None, dt)``, key frame
         first: the batched form of ``generate_sweeps``.  ``append_dt=False`` keeps F_out = F_in; with
         one transformed sweep per frame that is the reference's global rotation / scaling / flip
         (second/core/preprocess.py:756-804) applied in registers while the points are loaded.
+        ``crops``: optional list, one entry per frame, ``None`` or ``(normal_vec [K, 3], d [K])`` with
+        K <= 8 -- the surfaces of a convex polygon as the reference's ``surface_equ_3d`` returns them
+        (second/core/geometry.py:84-93); points with ``x*a + y*b + z*c + d >= 0`` for any surface are
+        dropped before the transform, which is ``remove_outside_points`` (box_np_ops.py:645-657).
         Returns ``(voxels [sum M, T, F_out], coors [sum M, 4], num_points, frame_voxel_offsets
         [B + 1][, mean])`` -- CUDA tensors for CUDA input, numpy arrays for numpy input."""
         import torch
@@ -305,6 +309,21 @@ class VoxelGenerator:
             total += n
             base += len(fr)
             so[i + 1] = base
+        carr = None
+        if crops is not None:
+            if len(crops) != b:
+                raise ValueError("crops needs one entry per frame")
+            carr = (_lib.BvxCrop * b)()
+            for i, cr in enumerate(crops):
+                if cr is None:
+                    continue
+                nv = np.asarray(cr[0], dtype=np.float64).reshape(-1, 3)
+                dd = np.asarray(cr[1], dtype=np.float64).reshape(-1)
+                if nv.shape[0] != dd.shape[0] or nv.shape[0] > 8:
+                    raise ValueError("a crop is (normal_vec [K, 3], d [K]) with K <= 8")
+                carr[i].n_planes = nv.shape[0]
+                for k in range(nv.shape[0]):
+                    carr[i].planes[k][:] = [nv[k, 0], nv[k, 1], nv[k, 2], dd[k]]
         f_out = f_in + (1 if append_dt else 0)
         h = self._ensure(total, max(b, nsw), max_voxels, f_out, dev.index)
         tt, cap = self._max_num_points, b * max_voxels
@@ -318,7 +337,7 @@ class VoxelGenerator:
             st = torch.cuda.current_stream(dev).cuda_stream
             _lib.check(_lib.load().bvx_generate_batched_sweeps(
                 h, arr, so.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), b, f_in, 1 if append_dt else 0,
-                max_voxels, voxels.data_ptr(), coors.data_ptr(), num.data_ptr(), fvo.data_ptr(),
+                carr, max_voxels, voxels.data_ptr(), coors.data_ptr(), num.data_ptr(), fvo.data_ptr(),
                 mean.data_ptr() if mean is not None else None, mean_channels, st), h)
             m = int(fvo[-1].item())
         out = (voxels[:m], coors[:m], num[:m], fvo) + ((mean[:m],) if mean is not None else ())

@@ -84,6 +84,20 @@ typedef struct bvx_sweep {
     float dt;              /* seconds, appended as channel f_in */
 } bvx_sweep;
 
+/* Optional convex crop of a frame's points, tested on the raw coordinates before
+ * the sweep transform: the reference's remove_outside_points
+ * (second/core/box_np_ops.py:645-657) -> points_in_convex_polygon_3d_jit
+ * (second/core/geometry.py:96-141).  planes[k] = (a, b, c, d) is one surface of
+ * the polygon as surface_equ_3d returns it (normal_vec, d), float64; a point
+ * with a*x + b*y + c*z + d >= 0 for any surface is dropped (evaluated in float64,
+ * left to right, like the reference's loop).  Dropping a point and compacting
+ * the array, as the reference does, gives the same voxels. */
+typedef struct bvx_crop {
+    int32_t n_planes;      /* 0 .. 8; 0 = no crop */
+    int32_t reserved;
+    double planes[8][4];
+} bvx_crop;
+
 /* Replaces spconv.utils.VoxelGenerator.__init__ as constructed at
  * second/builder/voxel_builder.py:23-27.  Allocates the workspace. */
 int bvx_create(const bvx_config* cfg, bvx_handle** out);
@@ -148,10 +162,13 @@ int bvx_generate_batched(bvx_handle* h, const float* points,
  * f_in + 1); append_dt == 0 keeps f_out = f_in -- with one transformed sweep
  * per frame this is the global rotation / scaling / flip of the reference's
  * augmentation (second/core/preprocess.py:756-804) fused into the point load.
+ * crops_host: NULL, or one bvx_crop per frame (the camera-frustum crop of
+ * remove_outside_points rides the same load).
  * Outputs as bvx_generate_batched with f = f_out. */
 int bvx_generate_batched_sweeps(bvx_handle* h, const bvx_sweep* sweeps_host,
                                 const int32_t* sweep_offsets_host, int32_t b,
                                 int32_t f_in, int32_t append_dt,
+                                const bvx_crop* crops_host,
                                 int32_t max_voxels, float* voxels,
                                 int32_t* coors4, int32_t* num_points,
                                 int32_t* frame_voxel_offsets,

@@ -230,3 +230,17 @@ def anchors_area(coors, anchors_bv, voxel_size, point_cloud_range, grid_sz):
     dm = sparse_sum_for_anchors_mask(coors, tuple(np.asarray(grid_sz)[::-1][1:]))
     _lib().orc_cumsum2d(_p(dm, _f32p), dm.shape[0], dm.shape[1])
     return fused_get_anchors_area(dm, anchors_bv, voxel_size, point_cloud_range, grid_sz)
+
+
+def crop_mask(points, normal_vec, d):
+    """second/core/geometry.py:122-141 (_points_in_convex_polygon_3d_jit for one polygon): float64,
+    sign = x*a + y*b + z*c + d summed left to right; a point is inside iff sign < 0 for every
+    surface.  ``normal_vec`` [K,3], ``d`` [K] as returned by the reference's surface_equ_3d."""
+    p = np.asarray(points, dtype=np.float32)[:, :3].astype(np.float64)
+    nv = np.asarray(normal_vec, dtype=np.float64).reshape(-1, 3)
+    dd = np.asarray(d, dtype=np.float64).reshape(-1)
+    inside = np.ones(p.shape[0], dtype=bool)
+    for k in range(nv.shape[0]):
+        sign = ((p[:, 0] * nv[k, 0] + p[:, 1] * nv[k, 1]) + p[:, 2] * nv[k, 2]) + dd[k]
+        inside &= ~(sign >= 0)
+    return inside

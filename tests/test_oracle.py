@@ -195,3 +195,13 @@ def test_anchors_area_is_a_box_count(oracle):
     y, x = coors[:, 1][None], coors[:, 2][None]
     want = ((x > c[:, 0:1]) & (x <= c[:, 2:3]) & (y > c[:, 1:2]) & (y <= c[:, 3:4])).sum(1)
     assert np.array_equal(got, want.astype(np.float32))
+
+
+def test_crop_mask_matches_reference_golden(oracle, golden_dir):
+    """The restated convex-polygon point test against outputs of the reference's own
+    points_in_convex_polygon_3d_jit (tests/golden/make_golden_crop.py)."""
+    z = np.load(os.path.join(golden_dir, "crop_reference.npz"))
+    for tag in ("front", "left"):
+        got = oracle.crop_mask(z[f"{tag}_points"], z[f"{tag}_normal_vec"], z[f"{tag}_d"])
+        assert got.dtype == bool and np.array_equal(got, z[f"{tag}_mask"])
+        assert 0 < got.sum() < got.size

@@ -241,6 +241,42 @@ def test_global_augmentation_fused_into_the_load(pkg, oracle, synth):
 
 
 @pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_frustum_crop_fused_into_the_load(pkg, oracle, synth, overflow, golden_dir):
+    """remove_outside_points (second/core/box_np_ops.py:645-657) as crop planes riding the point load:
+    dropping a point in the kernel must give the voxels the reference gets from the compacted array.
+    Planes and the points sitting exactly on them come from the golden file the reference's own
+    functions produced; one frame is also rotated after the crop, one is left uncropped."""
+    import os
+    z = np.load(os.path.join(golden_dir, "crop_reference.npz"))
+    g, o = _pair(pkg, oracle, KITTI, 5, 900, overflow)
+    frames, crops, want_frames = [], [], []
+    for i, tag in enumerate(("front", "left", None)):
+        if tag is None:
+            pts, crop = synth.lidar_frame(7000, "kitti", seed=77), None
+            keep = np.ones(pts.shape[0], bool)
+        else:
+            pts, crop = z[f"{tag}_points"], (z[f"{tag}_normal_vec"], z[f"{tag}_d"])
+            keep = oracle.crop_mask(pts, *crop)
+            assert np.array_equal(keep, z[f"{tag}_mask"])
+        R = _rot_z(0.2) if i == 1 else None
+        t = np.asarray([0.5, -0.25, 0.0], np.float32) if i == 1 else None
+        frames.append([(pts, R, t, 0.0)])
+        crops.append(crop)
+        kept = np.ascontiguousarray(pts[keep])                       # what the reference voxelizes
+        want_frames.append(np.ascontiguousarray(oracle.merge_sweeps([(kept, R, t, 0.0)])[:, :4]))
+    want = o.generate_batched(want_frames)
+    dev = [[(torch.from_numpy(np.ascontiguousarray(p)).cuda(), R, t, dt) for p, R, t, dt in sw] for sw in frames]
+    for _ in range(2):
+        gv, gc, gn, goff = g.generate_batched_sweeps(dev, append_dt=False, crops=crops)
+        assert np.array_equal(goff.cpu().numpy(), want[3])
+        _eq((gv, gc, gn), want[:3], "frustum crop")
+    with pytest.raises(ValueError):
+        g.generate_batched_sweeps(dev, append_dt=False, crops=crops[:2])
+    with pytest.raises(ValueError):
+        g.generate_batched_sweeps(dev, append_dt=False, crops=[(np.zeros((9, 3)), np.zeros(9)), None, None])
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
 def test_batched(pkg, oracle, synth, overflow):
     sizes = [5000, 0, 33, 12001, 1, 7000]
     frames = [synth.lidar_frame(n, "kitti", seed=40 + i) for i, n in enumerate(sizes)]
