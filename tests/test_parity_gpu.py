@@ -402,6 +402,45 @@ def test_pageable_after_pinned_keeps_streams(pkg, oracle, synth):
     _eq(g.generate_batched(hp, offs, out=out)[:3], want[:3], "pinned again, second call")
 
 
+@pytest.mark.parametrize("seed", range(6))
+def test_randomized_configurations(pkg, oracle, synth, seed):
+    """Seeded sweep over grids, caps, T, feature counts, batch shapes and both overflow rules, several
+    calls per handle (everything the pipeline empties for itself must really be empty again)."""
+    rng = np.random.default_rng(1000 + seed)
+    for _ in range(5):
+        vs = rng.choice([0.05, 0.1, 0.16, 0.25, 0.5, 1.0], 3).astype(np.float32)
+        vs[2] = rng.choice([0.1, 0.2, 0.5, 4.0])
+        cells = rng.integers(4, 400, 3)
+        lo = rng.uniform(-60, 0, 3).astype(np.float32)
+        rg = np.concatenate([lo, lo + vs * cells]).astype(np.float32)
+        T = int(rng.choice([1, 2, 3, 5, 8, 9, 12, 35]))
+        cap = int(rng.choice([1, 7, 100, 1000, 5000, 40000]))
+        f = int(rng.choice([3, 4, 4, 4, 5]))
+        overflow = str(rng.choice(["break", "continue"]))
+        g = pkg.VoxelGenerator(vs, rg, T, cap, overflow=overflow)
+        o = oracle.OracleVoxelGenerator(vs, rg, T, cap, overflow=overflow)
+        for _call in range(3):
+            b = int(rng.integers(1, 10))
+            frames = []
+            for _i in range(b):
+                n = int(rng.choice([0, 1, 31, 1024, 1025, 3000, 20000, 45000]))
+                pts = rng.uniform(rg[:3] - 2 * vs, rg[3:] + 2 * vs, (n, 3)).astype(np.float32)
+                if n and rng.random() < 0.5:                  # crowd a few cells
+                    pts[: n // 2] = pts[rng.integers(0, max(n // 50, 1), n // 2)] + \
+                        rng.uniform(0, 0.2, (n // 2, 3)).astype(np.float32) * vs
+                extra = rng.uniform(0, 1, (n, f - 3)).astype(np.float32)
+                frames.append(np.ascontiguousarray(np.concatenate([pts, extra], 1)))
+            want = o.generate_batched(frames)
+            cat = torch.from_numpy(np.concatenate(frames, 0)).cuda()
+            offs = np.concatenate([[0], np.cumsum([x.shape[0] for x in frames])]).astype(np.int32)
+            gv, gc, gn, goff = g.generate_batched(cat, offs)[:4]
+            what = f"seed={seed} vs={vs} T={T} cap={cap} f={f} {overflow} sizes={[x.shape[0] for x in frames]}"
+            assert np.array_equal(goff.cpu().numpy(), want[3]), what
+            _eq((gv, gc, gn), want[:3], what)
+            if b == 1:
+                _eq(g.generate(cat), o.generate(frames[0]), what + " single")
+
+
 def test_handle_growth_and_reuse(pkg, oracle, synth):
     g, o = _pair(pkg, oracle, KITTI, 5, 2000)
     for n in (1000, 50000, 200, 80000, 50000):
