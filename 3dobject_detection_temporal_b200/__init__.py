@@ -9,7 +9,7 @@ The directory name starts with a digit, so import it with
 """
 from . import _lib, synth  # noqa: F401
 from .builder import build as build_voxel_generator  # noqa: F401
-from .voxel_generator import VoxelGenerator, pinned_empty  # noqa: F401
+from .voxel_generator import VoxelGenerator, collate_points, pinned_empty  # noqa: F401
 from .shard import shard_frames  # noqa: F401
 
 

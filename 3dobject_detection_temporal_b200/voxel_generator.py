@@ -455,3 +455,22 @@ def pinned_empty(shape, dtype=np.float32):
 
 
 _PINNED = {}
+
+
+def collate_points(frames, pinned=True):
+    """Raw-points collate for the batched forms: per-sample ``[n_i, F]`` arrays ->
+    ``(points [sum n_i, F] float32, frame_offsets [B + 1] int32)``.  This is the point-cloud part of
+    what the reference's ``merge_second_batch`` does for voxels (concatenate in batch order;
+    second/pytorch/train.py:17,265) moved in front of the voxelizer; with ``pinned=True`` the batch
+    lands in pinned host memory, which ``generate_batched`` DMAs from in place (pipelined host form)."""
+    if len(frames) < 1:
+        raise ValueError("need at least one frame")
+    frames = [np.asarray(f, dtype=np.float32) for f in frames]
+    f = frames[0].shape[1]
+    if any(x.ndim != 2 or x.shape[1] != f for x in frames):
+        raise ValueError("frames must be [n_i, F] arrays with one feature count")
+    offs = np.concatenate([[0], np.cumsum([x.shape[0] for x in frames])]).astype(np.int32)
+    out = pinned_empty((int(offs[-1]), f), np.float32) if pinned else np.empty((int(offs[-1]), f), np.float32)
+    for x, a, b in zip(frames, offs[:-1], offs[1:]):
+        out[a:b] = x
+    return out, offs

@@ -125,3 +125,10 @@ def test_synth_is_deterministic(synth):
     assert a.dtype == np.float32 and a.shape == (5000, 4) and np.array_equal(a, b)
     assert np.isfinite(a).all()
     assert not np.array_equal(a, synth.lidar_frame(5000, "kitti", 4))
+
+
+def test_collate_points_pageable(pkg):
+    a = np.arange(12, dtype=np.float32).reshape(3, 4)
+    b = np.zeros((0, 4), np.float32)
+    pts, offs = pkg.collate_points([a, b, a[:1]], pinned=False)
+    assert offs.tolist() == [0, 3, 3, 4] and np.array_equal(pts[:3], a) and np.array_equal(pts[3], a[0])

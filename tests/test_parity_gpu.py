@@ -382,6 +382,19 @@ def test_prefix_upload_is_exact(pkg, oracle, synth):
     _eq((hv, hc, hn), want[:3], "prefix upload off")
 
 
+def test_collate_points_feeds_the_host_form(pkg, oracle, synth):
+    frames = [synth.lidar_frame(n, "kitti", seed=600 + i) for i, n in enumerate([4000, 0, 2500, 9000])]
+    pts, offs = pkg.collate_points(frames)
+    assert pts.shape == (15500, 4) and offs.tolist() == [0, 4000, 4000, 6500, 15500]
+    g, o = _pair(pkg, oracle, KITTI, 5, 1200)
+    want = o.generate_batched(frames)
+    got = g.generate_batched(pts, offs)
+    assert np.array_equal(got[3], want[3])
+    _eq(got[:3], want[:3], "collate_points -> generate_batched")
+    with pytest.raises(ValueError):
+        pkg.collate_points([frames[0], frames[0][:, :3]])
+
+
 def test_pageable_after_pinned_keeps_streams(pkg, oracle, synth):
     """Growing the pageable staging buffer must not disturb the pipelined form's streams and events."""
     cap = 1500
