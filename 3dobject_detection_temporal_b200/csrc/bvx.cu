@@ -69,6 +69,7 @@ struct bvx_handle {
     size_t pin_offs_count = 0;
     FrameState* pin_state = nullptr;   // per-frame results of the last pipelined host call
     size_t pin_state_count = 0;
+    bool pdl = getenv("BVX_NO_PDL") == nullptr;   // programmatic dependent launch between the pipeline kernels
     bool prefix_upload = true;         // break mode: upload only the prefix of a frame the cut-off can reach
     float cut_ratio = 0.f;             // largest (cut-off index / points) over the frames of the last call; 0 = unknown
     unsigned long long last_h2d = 0, last_d2h = 0;   // bytes moved by the last host-form call
@@ -453,7 +454,7 @@ struct Outputs {
     int frame_base;
 };
 
-// Launch with the table region marked L2-persisting (per-launch access policy window).
+// Pipeline kernels are launched with programmatic stream serialization (see pdl_prologue()).
 template <typename... KArgs, typename... Args>
 static void launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
                      cudaStream_t st, Args... args)
@@ -463,7 +464,11 @@ static void launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 bloc
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    (void)h;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = h->pdl ? 1 : 0;
     cudaLaunchKernelEx(&cfg, kern, args...);
     g_launches += 1;
 }

@@ -120,6 +120,16 @@ struct Pipe {
     int mean_c;
 };
 
+// Programmatic dependent launch: every pipeline kernel lets its successor start being scheduled as
+// soon as all of its own blocks are resident (the successor's blocks then fill the SM slots the last
+// wave frees), and itself waits here until its predecessor has completed and flushed.  Both
+// instructions are no-ops for a launch without the attribute.
+__device__ __forceinline__ void pdl_prologue()
+{
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ const SegDesc& find_seg(const Pipe& p, const FrameDesc& fr, int i)
 {
     int s = fr.seg_begin;
@@ -258,6 +268,7 @@ template <bool CROP>
 __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
 {
     __shared__ int s_chunk, s_ready;
+    pdl_prologue();
     const int f = blockIdx.x;
     const FrameDesc fr = p.frames[f];
     FrameState* st = p.state + f;
@@ -503,6 +514,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_verify(const Pipe p)
 {
     __shared__ int sm[kWarps + 1];
     __shared__ int s_last;
+    pdl_prologue();
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));   // prefix that went through k_insert
@@ -578,6 +590,7 @@ __device__ __forceinline__ unsigned int refind_first(const Pipe& p, const FrameD
 // k_insert: per round one atomic per point in flight.
 __global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
 {
+    pdl_prologue();
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     const int lim = min(p.state[f].n_done, p.state[f].istar);
@@ -740,6 +753,7 @@ template <int T>
 __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles)
 {
     extern __shared__ float4 smem_v[];
+    pdl_prologue();
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
@@ -813,6 +827,7 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
 __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int vt)
 {
     extern __shared__ int smem_i[];
+    pdl_prologue();
     const int f = blockIdx.y;
     const FrameDesc fr = p.frames[f];
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
