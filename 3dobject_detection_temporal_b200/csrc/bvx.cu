@@ -549,8 +549,11 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         ProfScope ps(h, 0, st);
         bool crop = false;
         for (const FrameSpec& fs : frames) crop |= fs.crop && fs.crop->n_planes > 0;
-        if (crop) launch_k(h, k_insert<true>, dim3(B, p.clear_rows + chunks), kBlock, 0, st, p);
-        else launch_k(h, k_insert<false>, dim3(B, p.clear_rows + chunks), kBlock, 0, st, p);
+        // persistent chunk rows: about as many blocks as the GPU holds at once (148 SMs x 8), never
+        // more rows than the largest frame has chunks
+        const int rows = std::min(chunks, std::max(1, (148 * 8 + B - 1) / B));
+        if (crop) launch_k(h, k_insert<true>, dim3(B, p.clear_rows + rows), kBlock, 0, st, p);
+        else launch_k(h, k_insert<false>, dim3(B, p.clear_rows + rows), kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);

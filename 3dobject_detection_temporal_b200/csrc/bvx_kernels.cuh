@@ -239,8 +239,8 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 }
 
 // ---------------------------------------------------------------- k_insert
-// grid (B, clear rows + max chunks per frame): x = frame, so blocks are dispatched row by
-// row across all frames: first the rows that clear the tables, then the chunk rows.  A block takes the frame's next chunk in index order
+// grid (B, clear rows + chunk rows): x = frame, so blocks are dispatched row by row across all
+// frames: first the rows that clear the tables, then the (persistent) chunk rows.  A block takes the frame's next chunk in index order
 // from a ticket counter.  Thread t of chunk c owns points c*1024 + k*256 + t,
 // k = 0..3: every warp-wide access is coalesced and a warp covers exactly one
 // 32-point mask word per k.
@@ -292,6 +292,10 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
     }
     if ((int)(blockIdx.y - p.clear_rows) * kChunk >= fr.n) return;
     const bool brk = !p.overflow_continue;
+    unsigned long long* tbl = p.table + fr.tbl_off;
+    // Chunk rows are persistent: a block keeps taking tickets of its frame until the frame is
+    // exhausted or cut, so the launch carries (rows x frames) blocks, not one block per chunk.
+  for (;;) {
     if (threadIdx.x == 0) {
         const unsigned long long t = atomicAdd(&st->ticket, 1ull);
         int c = (int)((unsigned int)t & 0x7FFFFFFFu);
@@ -304,9 +308,9 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
     }
     __syncthreads();
     const long long basel = (long long)s_chunk * kChunk;
+    const int ready = s_ready;
     if (basel >= fr.n) return;
     const int base = (int)basel;
-    unsigned long long* tbl = p.table + fr.tbl_off;
     int cell[kPts];
     unsigned int h[kPts];
 #pragma unroll
@@ -321,7 +325,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
     }
     unsigned int active = 0, needmin = 0, wonmask = 0;
     int nnew = 0;
-    if (!s_ready) {
+    if (!ready) {
         // The table must be empty before the first atomic (the point loads above did not need it).
         // The first block of a frame to see all clear rows done says so in bit 31 of the ticket
         // word; blocks that get the bit with their ticket skip this wait and its barrier.  (The clear
@@ -393,6 +397,8 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
         const int w = i >> 5;
         if ((threadIdx.x & 31) == 0 && w < fr.nwords) p.cand[fr.word_off + w] = b;
     }
+    __syncthreads();        // s_chunk / s_ready are rewritten by the next round
+  }
 }
 
 // ---------------------------------------------------------------- k_verify
