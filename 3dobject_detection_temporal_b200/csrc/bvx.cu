@@ -435,8 +435,15 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
     h->pin_next = (r + 1) % bvx_handle::kRing;
     CK(h, cudaEventSynchronize(h->pin_ev[r]));
     memcpy(h->pin[r], img.data(), img.size());
-    CK(h, cudaMemcpyAsync(h->d_frames, h->pin[r], fb, cudaMemcpyHostToDevice, st));
-    CK(h, cudaMemcpyAsync(h->d_segs, h->pin[r] + fb, sb, cudaMemcpyHostToDevice, st));
+    // The descriptors go to the device through a kernel that reads the pinned host buffer directly,
+    // not through the copy engine: a cudaMemcpyAsync of more than a few hundred bytes queues behind
+    // every bulk H2D copy already submitted (the pipelined host form has the whole batch in flight),
+    // which would hold this call's kernels back until all of them are done.
+    k_upload<<<1, kBlock, 0, st>>>(reinterpret_cast<const int*>(h->pin[r]), reinterpret_cast<int*>(h->d_frames),
+                                   (int)(fb / 4), reinterpret_cast<const int*>(h->pin[r] + fb),
+                                   reinterpret_cast<int*>(h->d_segs), (int)(sb / 4));
+    g_launches += 1;
+    CK(h, cudaGetLastError());
     CK(h, cudaEventRecord(h->pin_ev[r], st));
     h->uploaded.swap(img);
     return BVX_OK;

@@ -905,6 +905,16 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
     }
 }
 
+// ---------------------------------------------------------------- descriptor upload
+// One block copies the frame and segment descriptors of a call from the handle's pinned host
+// buffer (read over PCIe by the SM, no copy engine involved) into device memory.
+__global__ void __launch_bounds__(kBlock) k_upload(const int* __restrict__ src_a, int* __restrict__ dst_a, int na,
+                                                   const int* __restrict__ src_b, int* __restrict__ dst_b, int nb)
+{
+    for (int i = threadIdx.x; i < na; i += kBlock) dst_a[i] = src_a[i];
+    for (int i = threadIdx.x; i < nb; i += kBlock) dst_b[i] = src_b[i];
+}
+
 // ---------------------------------------------------------------- mean VFE
 // out[v, c] = sum_t voxels[v, t, c] / num[v]; tile of vt voxels staged in smem so
 // the [M, T, F] read is fully coalesced.  simple != 0: [ |xy|, z, refl ].
