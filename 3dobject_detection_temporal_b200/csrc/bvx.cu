@@ -793,9 +793,13 @@ static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::ve
               h->dev_offs_sub + (size_t)k * (fs + 1), nullptr, nullptr, 0, 4, f0};
     int rc = run_pipeline(h, fr, f, f, cap, o, st);
     if (rc) return rc;
-    CK(h, cudaMemcpyAsync(h->pin_offs + (size_t)k * (fs + 1), h->dev_offs_sub + (size_t)k * (fs + 1),
-                          ((size_t)bk + 1) * 4, cudaMemcpyDeviceToHost, st));
-    CK(h, cudaMemcpyAsync(h->pin_state + f0, h->d_state, (size_t)bk * sizeof(FrameState), cudaMemcpyDeviceToHost, st));
+    // offsets and per-frame state go home by SM stores into the pinned mirrors (same reason as the
+    // descriptor upload: a small cudaMemcpyAsync would wait for the bulk D2H copy in progress)
+    k_upload<<<1, kBlock, 0, st>>>(h->dev_offs_sub + (size_t)k * (fs + 1), h->pin_offs + (size_t)k * (fs + 1), bk + 1,
+                                   reinterpret_cast<const int*>(h->d_state), reinterpret_cast<int*>(h->pin_state + f0),
+                                   (int)((size_t)bk * sizeof(FrameState) / 4));
+    g_launches += 1;
+    CK(h, cudaGetLastError());
     h->last_d2h += ((size_t)bk + 1) * 4 + (size_t)bk * sizeof(FrameState);
     return BVX_OK;
 }
