@@ -522,6 +522,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.ovf = h->ovf;
     p.counters = h->counters;
     p.frame_voxel_offsets = o.frame_voxel_offsets ? o.frame_voxel_offsets : h->d_offsets_scratch;
+    p.voxel_num = o.voxel_num;
     p.nframes = B;
     p.f_in = f_in;
     p.f_out = f_out;
@@ -606,9 +607,6 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
             CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ProfScope ps(h, 5, st);
         launch_k(h, k_gather, dim3(tiles + rchunks, B), kBlock, smem, st, p, tiles, vt);
-    }
-    if (o.voxel_num) {
-        CK(h, cudaMemcpyAsync(o.voxel_num, p.frame_voxel_offsets + B, 4, cudaMemcpyDeviceToDevice, st));
     }
     CK(h, cudaGetLastError());
     return BVX_OK;

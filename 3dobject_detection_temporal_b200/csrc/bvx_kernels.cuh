@@ -101,6 +101,7 @@ struct Pipe {
     int2* ovf;
     int* counters;       // [0] frames-done ticket, [1] overflow count
     int* frame_voxel_offsets;
+    int* voxel_num;      // optional [1]: total number of voxels of the call
     int nframes;
     int f_in;
     int f_out;
@@ -508,6 +509,7 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, i
     }
     if (threadIdx.x == 0) {
         p.frame_voxel_offsets[p.nframes] = carry;
+        if (p.voxel_num) *p.voxel_num = carry;         // single-frame form: M for the caller
         p.counters[0] = 0;
         p.counters[1] = 0;
     }
