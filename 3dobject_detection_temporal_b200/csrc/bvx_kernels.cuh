@@ -163,6 +163,14 @@ __device__ __forceinline__ int cell_of(const GridParams& g, float x, float y, fl
     return ((int)cz * g.gs[1] + (int)cy) * g.gs[0] + (int)cx;
 }
 
+// L1-bypassing load of a table entry (the table is only ever modified by atomics, at the L2)
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* q)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(q) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ unsigned int hash_cell(unsigned int cell, int shift)
 {
     return (cell * 0x9E3779B1u) >> shift;
@@ -265,7 +273,7 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // are still table entries -- no pass over the table is needed to find them.  Every point
 // also records the first point of its cell as it saw it (slot[]); k_slot trusts that
 // record iff the recorded point is still a first point.
-template <bool CROP>
+template <bool CROP, bool PEEK>
 __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
 {
     __shared__ int s_chunk, s_ready;
@@ -324,7 +332,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
             cell[k] = cell_of(p.g, x, y, z);
         }
     }
-    unsigned int active = 0, needmin = 0, wonmask = 0;
+    unsigned int active = 0, needmin = 0, wonmask = 0, needcas = 0;
     int nnew = 0;
     if (!ready) {
         // The table must be empty before the first atomic (the point loads above did not need it).
@@ -354,9 +362,11 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
             const unsigned long long mine = ((unsigned long long)(unsigned)cell[k] << 32) |
                                             (unsigned)(base + k * kBlock + threadIdx.x);
             r[k] = 0;
-            if (active & (1u << k))
-                r[k] = (needmin & (1u << k)) ? atomicMin(tbl + h[k], mine)
-                                             : atomicCAS(tbl + h[k], kEmpty64, mine);
+            if (active & (1u << k)) {
+                if (needmin & (1u << k)) r[k] = atomicMin(tbl + h[k], mine);
+                else if (!PEEK || (needcas & (1u << k))) r[k] = atomicCAS(tbl + h[k], kEmpty64, mine);
+                else r[k] = ld_relaxed_u64(tbl + h[k]);      // PEEK: look before the atomic
+            }
         }
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
@@ -375,12 +385,19 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
                 }
                 active &= ~bit;
             } else if (r[k] == kEmpty64) {
-                wonmask |= bit; ++nnew; active &= ~bit;
-                h[k] = i;
+                if (PEEK && !(needcas & bit)) {
+                    needcas |= bit;                     // saw the slot empty: claim it next round
+                } else {
+                    wonmask |= bit; ++nnew; active &= ~bit;
+                    h[k] = i;
+                }
             } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
+                // (PEEK: a slot never changes its cell and its index only decreases, so an entry with a
+                // smaller index read by a plain load settles the point exactly as a failed CAS would)
                 if ((unsigned)r[k] > i) needmin |= bit; else { active &= ~bit; h[k] = (unsigned)r[k]; }
             } else {
                 h[k] = (h[k] + 1) & fr.tbl_mask;
+                if (PEEK) needcas &= ~bit;
             }
         }
     }
@@ -539,7 +556,19 @@ __global__ void __launch_bounds__(kBlock, 8) k_verify(const Pipe p)
         const int per = (total + gridDim.x - 1) / gridDim.x;
         const int lo = blockIdx.x * per, hi = min(total, lo + per);
         const int fill = chain ? kEmptyIdx : 0;
-        for (int j = lo + threadIdx.x; j < hi; j += kBlock) base[j] = fill;
+        if (hi > lo) {
+            // scalar head up to a 16-byte boundary, 16-byte stores, scalar tail
+            int* b0 = base + lo;
+            const int n = hi - lo;
+            const int head = min(n, (int)(((16u - (unsigned)((uintptr_t)b0 & 15u)) & 15u) >> 2));
+            if ((int)threadIdx.x < head) b0[threadIdx.x] = fill;
+            int4* b4 = reinterpret_cast<int4*>(b0 + head);
+            const int n4 = (n - head) >> 2;
+            const int4 f4 = make_int4(fill, fill, fill, fill);
+            for (int j = threadIdx.x; j < n4; j += kBlock) b4[j] = f4;
+            const int t0 = head + n4 * 4;
+            if ((int)threadIdx.x < n - t0) b0[t0 + threadIdx.x] = fill;
+        }
     }
     if (c0 >= nchunks && !(eff == 0 && blockIdx.x == 0)) return;
     const int nwords = (eff + 31) / 32;
