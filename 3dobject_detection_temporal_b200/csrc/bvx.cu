@@ -70,8 +70,6 @@ struct bvx_handle {
     FrameState* pin_state = nullptr;   // per-frame results of the last pipelined host call
     size_t pin_state_count = 0;
     bool pdl = getenv("BVX_NO_PDL") == nullptr;   // programmatic dependent launch between the pipeline kernels
-    bool peek = getenv("BVX_PEEK") != nullptr;               // k_insert looks at a slot before the atomic
-    bool small_table = getenv("BVX_SMALL_TABLE") != nullptr; // break mode: table sized by cap + chunks in flight
     int max_tbl_lg = 0;                // log2(slots) of the largest table of the current layout
     bool prefix_upload = true;         // break mode: upload only the prefix of a frame the cut-off can reach
     float cut_ratio = 0.f;             // largest (cut-off index / points) over the frames of the last call; 0 = unknown
@@ -335,14 +333,9 @@ struct FrameSpec {
 };
 
 // Chunk rows of k_insert = blocks of one frame in flight at a time (persistent; see run_pipeline).
-static int insert_rows_bound(int B)
-{
-    const char* e = getenv("BVX_INSERT_BLOCKS");
-    const int blocks = e ? std::max(1, atoi(e)) : 148 * 8;
-    return std::max(1, (blocks + B - 1) / B);
-}
+static int insert_rows_bound(int B) { return std::max(1, (148 * 8 + B - 1) / B); }
 
-static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st, int cap,
+static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
                          int* max_n_out, int* max_words_out, bool* all_aligned)
 {
     const int B = (int)frames.size();
@@ -412,13 +405,6 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
             if ((1ll << lg) > h->ncells && h->ncells >= 1024) {
                 // table never needs more slots than there are cells
                 lg = std::max(10, ilog2_ceil((unsigned long long)h->ncells + 1));
-            }
-            if (h->small_table && h->cfg.overflow_mode != BVX_OVERFLOW_CONTINUE) {
-                // Break mode: a chunk is only inserted if the count of claimed cells that came with its
-                // ticket was <= cap, and at most `rows` chunks of a frame are in flight, so the table
-                // never holds more than cap + rows * 1024 cells however many points the frame has.
-                const unsigned long long bound = (unsigned long long)cap + (unsigned long long)insert_rows_bound(B) * kChunk;
-                lg = std::min(lg, std::max(10, ilog2_ceil(bound + bound / 3 + 1)));
             }
             h->max_tbl_lg = std::max(h->max_tbl_lg, lg);
             fd.tbl_shift = 32 - lg;
@@ -521,7 +507,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     CK(h, cudaSetDevice(h->device));
     int max_n = 0, max_words = 0;
     bool aligned = true;
-    int rc = upload_layout(h, frames, st, cap, &max_n, &max_words, &aligned);
+    int rc = upload_layout(h, frames, st, &max_n, &max_words, &aligned);
     if (rc) return rc;
 
     Pipe p;
@@ -581,13 +567,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         // more rows than the largest frame has chunks
         const int rows = std::min(chunks, insert_rows_bound(B));
         const dim3 grid(B, p.clear_rows + rows);
-        if (crop) {
-            if (h->peek) launch_k(h, k_insert<true, true>, grid, kBlock, 0, st, p);
-            else launch_k(h, k_insert<true, false>, grid, kBlock, 0, st, p);
-        } else {
-            if (h->peek) launch_k(h, k_insert<false, true>, grid, kBlock, 0, st, p);
-            else launch_k(h, k_insert<false, false>, grid, kBlock, 0, st, p);
-        }
+        if (crop) launch_k(h, k_insert<true>, grid, kBlock, 0, st, p);
+        else launch_k(h, k_insert<false>, grid, kBlock, 0, st, p);
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);

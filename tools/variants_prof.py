@@ -11,7 +11,7 @@ frames = [pkg.synth.lidar_frame(c["n"], "kitti", i) for i in range(frames_n)]
 offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
 sets = [torch.from_numpy(np.concatenate([frames[(i + 7 * k) % frames_n] for i in range(frames_n)])).cuda()
         for k in range(3)]
-SW = ["BVX_PEEK", "BVX_SMALL_TABLE", "BVX_INSERT_BLOCKS"]
+SW = ["BVX_WARP_TICKETS", "BVX_SMALL_TABLE", "BVX_INSERT_BLOCKS", "BVX_ABLATE"]
 
 
 def run(env, overflow):
@@ -43,11 +43,5 @@ def run(env, overflow):
     gen.close()
 
 
-variants = [{}, {"BVX_PEEK": "1"}, {"BVX_SMALL_TABLE": "1"}, {"BVX_PEEK": "1", "BVX_SMALL_TABLE": "1"}]
 for ov in ("break", "continue"):
-    for v in variants:
-        run(v, ov)
-both = {"BVX_PEEK": "1", "BVX_SMALL_TABLE": "1"}
-for nb in (148 * 4, 148 * 6):
-    run(dict(both, BVX_INSERT_BLOCKS=str(nb)), "break")
-run({}, "break")
+    run({}, ov)
