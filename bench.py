@@ -303,13 +303,13 @@ def run_ours(args):
     pipe_bytes = sum(ab.values())
     pipe_gbs = pipe_bytes / (ms_step * 1e-3) / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
-    # capture of this workload (profiles/r01_d_ncu_full_summary.txt); cold L2, cfg4 with 64 frames only
-    ncu_traffic = {"k_insert": 62.64e6 + 64.73e6, "k_verify": 0.99e6 + 0.00e6,
-                   "k_slot": 29.60e6 + 4.20e6, "k_gather": 74.97e6 + 97.35e6}
+    # capture of this workload (profiles/r01_f_ncu_full_summary.txt); cold L2, cfg4 with 64 frames only
+    ncu_traffic = {"k_insert": 66.47e6 + 66.16e6, "k_verify": 1.05e6 + 0.00e6,
+                   "k_slot": 30.41e6 + 4.14e6, "k_gather": 74.95e6 + 96.87e6}
     traffic = ncu_traffic.get(dom) if (B == 64 and args.overflow == "break") else None
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/r01_d_ncu_full_summary.txt (ncu --set full, cold L2)",
+                "traffic_source": "profiles/r01_f_ncu_full_summary.txt (ncu --set full, cold L2)",
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": dom_bytes,
                 "kernel_ms": per_kernel[dom], "kernel_share_of_step": per_kernel[dom] / ksum,
