@@ -81,6 +81,7 @@ SYMBOLS = {
     "bvx_host_alloc": (ctypes.c_int, [ctypes.POINTER(_vp), ctypes.c_size_t]),
     "bvx_host_free": (ctypes.c_int, [_vp]),
     "bvx_set_prefix_upload": (ctypes.c_int, [_vp, _i32]),
+    "bvx_set_host_assemble": (ctypes.c_int, [_vp, _i32]),
     "bvx_last_transfer": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64),
                                          ctypes.POINTER(_i32)]),
     "bvx_mean_vfe": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),

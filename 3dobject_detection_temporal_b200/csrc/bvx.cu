@@ -17,12 +17,82 @@
 
 #include "bvx.h"
 #include "bvx_kernels.cuh"
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#include <xmmintrin.h>
+#endif
+#include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include "bvx_anchors.cuh"
 
 using namespace bvx;
 
 static std::atomic<long long> g_launches{0};
 static thread_local std::string g_last_error;
+
+// Fork-join pool of host threads for the host form's row assembly (see assemble_rows): the
+// workers sleep on a condition variable between jobs; the calling thread takes share 0.
+struct HostPool {
+    std::vector<std::thread> workers;
+    std::mutex mu;
+    std::condition_variable cv_go, cv_done;
+    std::function<void(int, int)> job;   // (share, shares)
+    long long generation = 0;
+    int pending = 0;
+    bool stop = false;
+    int shares = 1;
+
+    void start(int n)
+    {
+        shares = std::max(1, n);
+        for (int w = 1; w < shares; ++w)
+            workers.emplace_back([this, w] {
+                long long seen = 0;
+                for (;;) {
+                    std::function<void(int, int)> fn;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        cv_go.wait(lk, [&] { return stop || generation != seen; });
+                        if (stop) return;
+                        seen = generation;
+                        fn = job;
+                    }
+                    fn(w, shares);
+                    {
+                        std::lock_guard<std::mutex> lk(mu);
+                        if (--pending == 0) cv_done.notify_one();
+                    }
+                }
+            });
+    }
+    void run(const std::function<void(int, int)>& fn)
+    {
+        if (shares > 1) {
+            std::lock_guard<std::mutex> lk(mu);
+            job = fn;
+            pending = shares - 1;
+            ++generation;
+            cv_go.notify_all();
+        }
+        fn(0, shares);
+        if (shares > 1) {
+            std::unique_lock<std::mutex> lk(mu);
+            cv_done.wait(lk, [&] { return pending == 0; });
+        }
+    }
+    ~HostPool()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            stop = true;
+            cv_go.notify_all();
+        }
+        for (auto& t : workers) t.join();
+    }
+};
 
 struct bvx_handle {
     bvx_config cfg;
@@ -57,8 +127,8 @@ struct bvx_handle {
     std::vector<SegDesc> h_segs;
     std::vector<char> uploaded;  // byte image of the last uploaded layout
     bool all_plain = false;      // every frame of the current layout is one plain segment
-    static const int kRing = 4;
-    char* pin[kRing] = {nullptr, nullptr, nullptr, nullptr};
+    static const int kRing = 16;   // >= sub-batches of a pipelined host call, so enqueueing them never waits for the device
+    char* pin[kRing] = {};
     cudaEvent_t pin_ev[kRing];
     size_t pin_bytes = 0;
     int pin_next = 0;
@@ -72,6 +142,12 @@ struct bvx_handle {
     bool pdl = getenv("BVX_NO_PDL") == nullptr;   // programmatic dependent launch between the pipeline kernels
     int max_tbl_lg = 0;                // log2(slots) of the largest table of the current layout
     bool prefix_upload = true;         // break mode: upload only the prefix of a frame the cut-off can reach
+    bool host_assemble = true;         // pipelined host form: bring home point indices, assemble the padded rows on the host
+    HostPool* pool = nullptr;          // host threads of the row assembly (created on first use)
+    int* dev_idx = nullptr;            // [voxel capacity, T] point index per (voxel, slot) of the host form
+    int32_t* pin_idx = nullptr;        // pinned mirror of dev_idx
+    size_t pin_idx_count = 0;
+    std::vector<cudaEvent_t> ev_out;   // per sub-batch: its D2H copies have landed
     float cut_ratio = 0.f;             // largest (cut-off index / points) over the frames of the last call; 0 = unknown
     unsigned long long last_h2d = 0, last_d2h = 0;   // bytes moved by the last host-form call
     int last_redo = 0;                 // sub-batches of the last call that had to be redone with full frames
@@ -212,6 +288,10 @@ extern "C" int bvx_destroy(bvx_handle* h)
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
     for (cudaEvent_t e : h->ev_h2d) cudaEventDestroy(e);
     for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->ev_out) cudaEventDestroy(e);
+    delete h->pool;
+    cudaFree(h->dev_idx);
+    if (h->pin_idx) cudaFreeHost(h->pin_idx);
     if (h->pin_offs) cudaFreeHost(h->pin_offs);
     if (h->pin_state) cudaFreeHost(h->pin_state);
     if (h->stage_in) cudaFreeHost(h->stage_in);
@@ -465,6 +545,7 @@ struct Outputs {
     int mean_c;
     int coor_cols;
     int frame_base;
+    int32_t* idx = nullptr;        // optional [sum M, T] point indices (host form); voxels may then be null
 };
 
 // Pipeline kernels are launched with programmatic stream serialization (see pdl_prologue()).
@@ -498,7 +579,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     const int cap = max_voxels > 0 ? max_voxels : h->cfg.max_voxels;
     if (cap > h->cfg.max_voxels)
         return fail(h, BVX_ERR_WORKSPACE, "max_voxels=%d exceeds the handle capacity %d", cap, h->cfg.max_voxels);
-    if (!o.voxels || !o.coors || !o.num_points)
+    if ((!o.voxels && !o.idx) || !o.coors || !o.num_points)
         return fail(h, BVX_ERR_BAD_ARGUMENT, "null output pointer");
     if (((uintptr_t)o.voxels & 15) || ((uintptr_t)o.coors & 15))
         return fail(h, BVX_ERR_BAD_ARGUMENT, "voxels/coors must be 16-byte aligned");
@@ -541,6 +622,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
     p.clear_rows = 0;
     p.voxels = o.voxels;
+    p.idx_out = o.idx;
     p.coors = o.coors;
     p.num_points = o.num_points;
     p.mean_out = o.mean;
@@ -783,7 +865,7 @@ static int stage_out(bvx_handle* h, void* dst[3], const void* src[3], const size
 // Kernels of sub-batch k (frames [f0, f1), the first pre[f] points of each) on st, then the
 // D2H of its offsets and per-frame state into the pinned mirrors.
 static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::vector<int>& pre, int f0, int f1,
-                               int k, int fs, int f, int cap, cudaStream_t st)
+                               int k, int fs, int f, int cap, bool assemble, cudaStream_t st)
 {
     const int T = h->cfg.max_num_points;
     const int bk = f1 - f0;
@@ -796,6 +878,10 @@ static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::ve
     const size_t v0 = (size_t)f0 * cap;
     Outputs o{h->dev_voxels + v0 * T * f, h->dev_coors + v0 * 4, h->dev_num + v0,
               h->dev_offs_sub + (size_t)k * (fs + 1), nullptr, nullptr, 0, 4, f0};
+    if (assemble) {            // indices instead of rows: the host assembles the rows (assemble_rows)
+        o.voxels = nullptr;
+        o.idx = h->dev_idx + v0 * T;
+    }
     int rc = run_pipeline(h, fr, f, f, cap, o, st);
     if (rc) return rc;
     // offsets and per-frame state go home by SM stores into the pinned mirrors (same reason as the
@@ -807,6 +893,55 @@ static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::ve
     CK(h, cudaGetLastError());
     h->last_d2h += ((size_t)bk + 1) * 4 + (size_t)bk * sizeof(FrameState);
     return BVX_OK;
+}
+
+// Host half of the pipelined host form.  The padded [M, T, f] rows are 4-5x their information
+// (cfg4: 1.2 points per voxel in T = 5 slots) and the PCIe link is what bounds the call, so only
+// the frame-local point index of every kept (voxel, slot) comes home (4*T bytes per voxel instead
+// of 4*T*f); the rows are copied here from the caller's own points, zero padded, by the handle's
+// host threads, while the copies and kernels of the next sub-batch run.  Every row of the
+// reference's voxels is a verbatim copy of an input row, so this is bit-exact by construction.
+// Voxels [run0, run0 + m) are those of frames [f0, f1); fvo = global voxel offsets per frame.
+static void assemble_rows(bvx_handle* h, const float* points, const int32_t* offs, const int32_t* fvo, int f0, int f1,
+                          size_t run0, size_t m, int T, int f, float* voxels, const int32_t* num_points,
+                          const int32_t* idx)
+{
+    if (m == 0) return;
+    h->pool->run([=](int share, int shares) {
+        const size_t per = (m + shares - 1) / shares;
+        const size_t lo = run0 + std::min(m, per * share), hi = run0 + std::min(m, per * (share + 1));
+        int fi = f0;
+        for (size_t gv = lo; gv < hi; ++gv) {
+            while (fi + 1 < f1 && (size_t)fvo[fi + 1] <= gv) ++fi;
+            const float* src = points + (size_t)offs[fi] * f;
+            const int n = num_points[gv];
+            const int32_t* id = idx + gv * T;
+            float* dst = voxels + gv * (size_t)T * f;
+#if defined(__SSE2__)
+            if (f == 4 && ((((uintptr_t)voxels) | ((uintptr_t)points)) & 15) == 0) {
+                // 16-byte rows: streaming stores (the output is written once and not read here, so no
+                // read-for-ownership of its lines), and the first row of a voxel a few voxels ahead is
+                // prefetched -- the row reads are random accesses into the caller's points
+                constexpr size_t kAhead = 24;
+                if (gv + kAhead < hi) {
+                    int fa = fi;
+                    while (fa + 1 < f1 && (size_t)fvo[fa + 1] <= gv + kAhead) ++fa;
+                    const int ia = idx[(gv + kAhead) * T];
+                    if (ia >= 0) _mm_prefetch((const char*)(points + ((size_t)offs[fa] + ia) * 4), _MM_HINT_T0);
+                }
+                const __m128 zero = _mm_setzero_ps();
+                for (int t = 0; t < n; ++t) _mm_stream_ps(dst + 4 * t, _mm_load_ps(src + 4 * (size_t)id[t]));
+                for (int t = n; t < T; ++t) _mm_stream_ps(dst + 4 * t, zero);
+                continue;
+            }
+#endif
+            for (int t = 0; t < n; ++t) memcpy(dst + (size_t)t * f, src + (size_t)id[t] * f, (size_t)f * 4);
+            if (n < T) memset(dst + (size_t)n * f, 0, (size_t)(T - n) * f * 4);
+        }
+#if defined(__SSE2__)
+        _mm_sfence();
+#endif
+    });
 }
 
 static int generate_batched_pipelined(bvx_handle* h, const float* points, const int32_t* offs, int b, int f,
@@ -828,6 +963,29 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         cudaEvent_t e;
         CK(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         h->ev_done.push_back(e);
+    }
+    const bool assemble = h->host_assemble;
+    if (assemble) {
+        if (!h->pool) {
+            h->pool = new HostPool();
+            h->pool->start((int)std::min(32u, std::max(1u, std::thread::hardware_concurrency())));
+        }
+        while ((int)h->ev_out.size() < ns) {
+            cudaEvent_t e;
+            CK(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            h->ev_out.push_back(e);
+        }
+        const size_t cnt = (size_t)b * cap * T;
+        if (cnt > h->pin_idx_count) {
+            if (h->pin_idx) cudaFreeHost(h->pin_idx);
+            h->pin_idx = nullptr;
+            cudaFree(h->dev_idx);
+            h->dev_idx = nullptr;
+            h->pin_idx_count = 0;
+            CK(h, cudaMallocHost((void**)&h->pin_idx, cnt * 4));
+            CK(h, cudaMalloc((void**)&h->dev_idx, cnt * 4));
+            h->pin_idx_count = cnt;
+        }
     }
     const size_t need = (size_t)ns * (fs + 1);
     if (need > h->pin_offs_count) {
@@ -882,20 +1040,31 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         }
         CK(h, cudaEventRecord(h->ev_h2d[k], h->s_h2d));
     }
+    // (Letting the DMA engine bring the rows of every second / third / fourth sub-batch while the threads
+    // assemble the others measured slower than assembling all of them: 3.5 / 3.0 / 2.85 vs 2.87 ms.)
+    const std::vector<char> asm_k(ns, assemble ? 1 : 0);
     // leg 2: the kernels of each sub-batch on the caller's stream, outputs at capacity stride
     for (int k = 0; k < ns; ++k) {
         const int f0 = k * fs, f1 = std::min(b, f0 + fs);
         CK(h, cudaStreamWaitEvent(st, h->ev_h2d[k], 0));
-        int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, st);
+        int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, asm_k[k] != 0, st);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev_done[k], st));
     }
     // leg 3: as each sub-batch finishes, its M rows go home on the copy-out stream
+    const bool trace = getenv("BVX_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::micro>(b - a).count(); };
+    double t_done = 0, t_out = 0, t_asm = 0;
+    const auto t_leg3 = now();
+    std::vector<size_t> sub_run(ns, 0), sub_m(ns, 0);
+    int pending = -1;
     size_t run = 0;
     fvo_host[0] = 0;
     for (int k = 0; k < ns; ++k) {
         const int f0 = k * fs, f1 = std::min(b, f0 + fs), bk = f1 - f0;
-        CK(h, cudaEventSynchronize(h->ev_done[k]));
+        { const auto a = now(); CK(h, cudaEventSynchronize(h->ev_done[k])); t_done += us(a, now()); }
         bool redo = false;
         for (int i = f0; i < f1; ++i)
             if (pre[i] < offs[i + 1] - offs[i] && !(h->pin_state[i].total > cap)) redo = true;
@@ -910,7 +1079,7 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
                 h->last_h2d += (size_t)(n - pre[i]) * f * 4;
                 pre[i] = n;
             }
-            int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, st);
+            int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, asm_k[k] != 0, st);
             if (rc) return rc;
             CK(h, cudaStreamSynchronize(st));
             h->last_redo += 1;
@@ -919,14 +1088,44 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         const size_t m = (size_t)lo[bk], v0 = (size_t)f0 * cap;
         for (int i = 1; i <= bk; ++i) fvo_host[f0 + i] = (int32_t)(run + (size_t)lo[i]);
         if (m > 0) {
-            CK(h, cudaMemcpyAsync(voxels + run * T * f, h->dev_voxels + v0 * T * f, m * T * f * 4,
-                                  cudaMemcpyDeviceToHost, h->s_d2h));
+            if (asm_k[k])
+                CK(h, cudaMemcpyAsync(h->pin_idx + run * T, h->dev_idx + v0 * T, m * T * 4, cudaMemcpyDeviceToHost,
+                                      h->s_d2h));
+            else
+                CK(h, cudaMemcpyAsync(voxels + run * T * f, h->dev_voxels + v0 * T * f, m * T * f * 4,
+                                      cudaMemcpyDeviceToHost, h->s_d2h));
             CK(h, cudaMemcpyAsync(coors4 + run * 4, h->dev_coors + v0 * 4, m * 16, cudaMemcpyDeviceToHost, h->s_d2h));
             CK(h, cudaMemcpyAsync(num_points + run, h->dev_num + v0, m * 4, cudaMemcpyDeviceToHost, h->s_d2h));
-            h->last_d2h += m * ((size_t)T * f * 4 + 16 + 4);
+            h->last_d2h += m * ((size_t)T * (asm_k[k] ? 1 : f) * 4 + 16 + 4);
+        }
+        sub_run[k] = run; sub_m[k] = m;
+        if (assemble) {
+            // the sub-batch whose indices came home last is assembled while this one's copies are in flight
+            CK(h, cudaEventRecord(h->ev_out[k], h->s_d2h));
+            if (pending >= 0) {
+                { const auto a = now(); CK(h, cudaEventSynchronize(h->ev_out[pending])); t_out += us(a, now()); }
+                const int g0 = pending * fs, g1 = std::min(b, g0 + fs);
+                const auto a = now();
+                assemble_rows(h, points, offs, fvo_host, g0, g1, sub_run[pending], sub_m[pending], T, f, voxels,
+                              num_points, h->pin_idx);
+                t_asm += us(a, now());
+                pending = -1;
+            }
+            if (asm_k[k]) pending = k;
         }
         run += m;
     }
+    if (pending >= 0) {
+        { const auto a = now(); CK(h, cudaEventSynchronize(h->ev_out[pending])); t_out += us(a, now()); }
+        const int g0 = pending * fs, g1 = std::min(b, g0 + fs);
+        const auto a = now();
+        assemble_rows(h, points, offs, fvo_host, g0, g1, sub_run[pending], sub_m[pending], T, f, voxels, num_points,
+                      h->pin_idx);
+        t_asm += us(a, now());
+    }
+    if (trace)
+        fprintf(stderr, "[bvx] leg3 %.0f us: wait kernels %.0f, wait copies %.0f, assemble %.0f (%d threads)\n",
+                us(t_leg3, now()), t_done, t_out, t_asm, h->pool ? h->pool->shares : 0);
     // where the cut-offs were this time: the next call's prefix
     if (brk) {
         float r = 0.f;
@@ -1007,6 +1206,13 @@ extern "C" int bvx_set_prefix_upload(bvx_handle* h, int32_t on)
     if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
     h->prefix_upload = on != 0;
     h->cut_ratio = 0.f;
+    return BVX_OK;
+}
+
+extern "C" int bvx_set_host_assemble(bvx_handle* h, int32_t on)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    h->host_assemble = on != 0;
     return BVX_OK;
 }
 

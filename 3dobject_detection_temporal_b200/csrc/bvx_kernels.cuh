@@ -114,6 +114,9 @@ struct Pipe {
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
     int clear_rows;      // hashed tables: the first clear_rows block rows of k_insert clear the tables (0: dense grid)
     // outputs
+    int* idx_out;        // optional [sum M, T]: frame-local point index of every kept (voxel, slot), -1 = empty.
+                         // With it, voxels may be null: the host form assembles the rows from its own copy
+                         // of the points (the padded rows are 4-5x their information and PCIe is the bound)
     float* voxels;
     int* coors;
     int* num_points;
@@ -816,27 +819,33 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
             ++nvalid;
         }
     }
-    // per-warp transpose: voxel-major float4 index lane*T + s, read back linearly
-    float4* sw = smem_v + wid * (32 * T);
+    if (p.voxels) {
+        // per-warp transpose: voxel-major float4 index lane*T + s, read back linearly
+        float4* sw = smem_v + wid * (32 * T);
 #pragma unroll
-    for (int s = 0; s < T; ++s) {
-        int q = lane * T + s;
-        if ((T & 1) == 0) q ^= (q >> 3) & 7;
-        sw[q] = row[s];
-    }
-    __syncwarp();
-    const int wv0 = v0 + wid * 32;                    // first voxel of this warp
-    const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
-    float4* out = reinterpret_cast<float4*>(p.voxels) + (gbase + wv0) * T;
+        for (int s = 0; s < T; ++s) {
+            int q = lane * T + s;
+            if ((T & 1) == 0) q ^= (q >> 3) & 7;
+            sw[q] = row[s];
+        }
+        __syncwarp();
+        const int wv0 = v0 + wid * 32;                    // first voxel of this warp
+        const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
+        float4* out = reinterpret_cast<float4*>(p.voxels) + (gbase + wv0) * T;
 #pragma unroll
-    for (int s = 0; s < T; ++s) {
-        const int j = s * 32 + lane;
-        int q = j;
-        if ((T & 1) == 0) q ^= (q >> 3) & 7;
-        if (j < wn * T) __stcs(out + j, sw[q]);
+        for (int s = 0; s < T; ++s) {
+            const int j = s * 32 + lane;
+            int q = j;
+            if ((T & 1) == 0) q ^= (q >> 3) & 7;
+            if (j < wn * T) __stcs(out + j, sw[q]);
+        }
     }
     if (!live) return;
     const size_t gv = gbase + v;
+    if (p.idx_out) {
+#pragma unroll
+        for (int s = 0; s < T; ++s) p.idx_out[gv * T + s] = idx[s] == kEmptyIdx ? -1 : idx[s];
+    }
     p.num_points[gv] = nvalid;
     write_coor(p, f, gv, cell_of(p.g, row[0].x, row[0].y, row[0].z));
     if (p.mean_out) {
@@ -905,18 +914,22 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
             for (int k = 0; k < nvalid; ++k) r += (vb[k] < my);   // slot = rank of the index in the voxel
             float* dst = srow + (size_t)(v * T + r) * F;
             fetch_row(p, fr, my, dst);
+            if (p.idx_out) p.idx_out[(gout + v) * T + r] = my;
             if (r == 0) write_coor(p, f, gout + v, cell_of(p.g, dst[0], dst[1], dst[2]));
         }
         if (s >= nvalid) {
             float* z = srow + (size_t)(v * T + s) * F;
             for (int k = 0; k < F; ++k) z[k] = 0.0f;
+            if (p.idx_out) p.idx_out[(gout + v) * T + s] = -1;
         }
         if (s == 0) p.num_points[gout + v] = nvalid;
     }
     __syncthreads();
     float* out = p.voxels + gout * T * F;
     const int tot = E * F;
-    if ((tot & 3) == 0 && ((((size_t)gout * T * F) & 3) == 0)) {
+    if (!p.voxels) {
+        // rows are assembled by the host from idx_out
+    } else if ((tot & 3) == 0 && ((((size_t)gout * T * F) & 3) == 0)) {
         float4* o4 = reinterpret_cast<float4*>(out);
         const float4* s4 = reinterpret_cast<const float4*>(srow);
         for (int k = threadIdx.x; k < (tot >> 2); k += kBlock) __stcs(o4 + k, s4[k]);

@@ -34,7 +34,7 @@ def _is_torch(x):
 
 class VoxelGenerator:
     def __init__(self, voxel_size, point_cloud_range, max_num_points, max_voxels=20000,
-                 overflow="break", grid="hashed", device=None, prefix_upload=True):
+                 overflow="break", grid="hashed", device=None, prefix_upload=True, host_assemble=True):
         if overflow not in _lib.OVERFLOW:
             raise ValueError(f"overflow must be 'break' or 'continue', got {overflow!r}")
         if grid not in _lib.GRID:
@@ -49,6 +49,7 @@ class VoxelGenerator:
         self._grid = grid
         self._device = device
         self._prefix_upload = bool(prefix_upload)
+        self._host_assemble = bool(host_assemble)
         lib = _lib.load()
         gs = (ctypes.c_int64 * 3)()
         _lib.check(lib.bvx_grid_size(
@@ -123,6 +124,8 @@ class VoxelGenerator:
         _lib.check(_lib.load().bvx_create(ctypes.byref(cfg), ctypes.byref(h)))
         if not self._prefix_upload:
             _lib.check(_lib.load().bvx_set_prefix_upload(h, 0), h)
+        if not self._host_assemble:
+            _lib.check(_lib.load().bvx_set_host_assemble(h, 0), h)
         self._handle = h
         self._cap = cap
         return h

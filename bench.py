@@ -318,7 +318,7 @@ def run_ours(args):
                              "frac": pipe_gbs / peak}}
 
     # ---- end to end through the host-buffer call: pinned numpy in, pinned numpy out
-    e2e = e2e_full = None
+    e2e = e2e_full = e2e_rows = None
     if not args.no_e2e:
         hp = pkg.pinned_empty(host.shape, np.float32)
         hp[:] = host
@@ -326,9 +326,9 @@ def run_ours(args):
                 pkg.pinned_empty((B * cap,), np.int32), pkg.pinned_empty((B + 1,), np.int32))
         ksteps = max(3, min(args.steps, 20))
 
-        def host_arm(prefix_upload):
+        def host_arm(prefix_upload, host_assemble=True):
             gen_h = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=args.overflow,
-                                       device=dev, prefix_upload=prefix_upload)
+                                       device=dev, prefix_upload=prefix_upload, host_assemble=host_assemble)
             for _ in range(3):
                 r = gen_h.generate_batched(hp, offs, out=hout)
             if world > 1:
@@ -351,12 +351,17 @@ def run_ours(args):
                     "api": "VoxelGenerator.generate_batched(numpy) -> bvx_generate_batched_host; pinned host "
                            "buffers" + ("; break mode uploads only the prefix of each frame the cut-off can reach "
                                         "(sized from the previous call, verified per frame, redone if short)"
-                                        if prefix_upload and args.overflow == "break" else "; whole frames uploaded"),
+                                        if prefix_upload and args.overflow == "break" else "; whole frames uploaded")
+                           + ("; point indices come home (4*T bytes per voxel), the padded rows are assembled from "
+                              "the caller's points by the handle's host threads" if host_assemble else
+                              "; padded rows gathered on the device and copied home"),
+                    "host_threads": min(32, os.cpu_count() or 1) if host_assemble else 0,
                     "host_numa_binding": numa}
 
         e2e = host_arm(True)
+        e2e_rows = host_arm(True, host_assemble=False)
         if args.overflow == "break":
-            e2e_full = host_arm(False)
+            e2e_full = host_arm(False, host_assemble=False)
     clocks = sampler.stop() if rank == 0 else None
 
     cpu = None
@@ -373,7 +378,7 @@ def run_ours(args):
                            "voxels_per_gpu": m_voxels, "kept_points_per_gpu": kept, "overflow": args.overflow,
                            "l2": f"inputs rotate over {NSETS} distinct {host.nbytes >> 20} MiB batches "
                                  "(> 126 MB L2); outputs rewritten every step; no explicit flush"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_full_upload": e2e_full,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_device_rows": e2e_rows, "e2e_full_upload": e2e_full,
                 "gpu_launches": int(launches),
                 "clocks": clocks}
         print(json.dumps(line))

@@ -319,6 +319,45 @@ def test_batched_host_pipelined(pkg, oracle, synth, overflow):
             _eq((hv, hc, hn), (wv, wc, wn), f"pipelined host {sizes[:3]}")
 
 
+@pytest.mark.parametrize("T,f", [(5, 4), (3, 5), (35, 4), (12, 7)])
+@pytest.mark.parametrize("assemble", [True, False])
+def test_host_assembly_matches_device_rows(pkg, oracle, synth, T, f, assemble):
+    """Pinned batched host form with host assembly (point indices come home, the padded rows are
+    copied from the caller's points by host threads) against the oracle, for the specialised
+    gather (T <= 8, 4 features) and the general one (long buckets, other feature counts), ragged
+    batches with empty frames, crowded voxels; and the same with the device-side rows."""
+    rng = np.random.default_rng(T * 100 + f)
+    cfg = dict(voxel_size=[0.4, 0.4, 0.8], point_cloud_range=[0, -40, -3, 70.4, 40, 1])
+    cap = 900
+    sizes = [7000, 0, 1, 9000, 350, 0, 12000, 5000, 2, 3000, 8000]
+    frames = []
+    for i, n in enumerate(sizes):
+        p4 = synth.lidar_frame(n, "kitti", seed=300 + i)
+        extra = rng.normal(0, 1, size=(n, f - 4)).astype(np.float32) if f > 4 else np.zeros((n, 0), np.float32)
+        frames.append(np.ascontiguousarray(np.concatenate([p4, extra], axis=1)[:, :f]))
+    for overflow in ("break", "continue"):
+        g = pkg.VoxelGenerator(cfg["voxel_size"], cfg["point_cloud_range"], T, cap, overflow=overflow,
+                               host_assemble=assemble)
+        o = oracle.OracleVoxelGenerator(cfg["voxel_size"], cfg["point_cloud_range"], T, cap, overflow)
+        wv, wc, wn, woff = o.generate_batched(frames)
+        cat = np.concatenate(frames, axis=0)
+        offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+        hp = pkg.pinned_empty(cat.shape, np.float32)
+        hp[:] = cat
+        b = len(sizes)
+        out = (pkg.pinned_empty((b * cap, T, f), np.float32), pkg.pinned_empty((b * cap, 4), np.int32),
+               pkg.pinned_empty((b * cap,), np.int32), pkg.pinned_empty((b + 1,), np.int32))
+        for rep in range(3):
+            out[0][:] = np.float32(7.0)                 # stale rows must be overwritten, padding included
+            hv, hc, hn, hoff = g.generate_batched(hp, offs, out=out)
+            assert np.array_equal(hoff, woff)
+            _eq((hv, hc, hn), (wv, wc, wn), f"host assembly={assemble} T={T} f={f} {overflow} rep {rep}")
+        h2d, d2h, _ = g.last_transfer()
+        m = int(woff[-1])
+        assert d2h < m * (T * (4 if assemble else 4 * f) + 20) + 4096
+        g.close()
+
+
 def _pinned_batch(pkg, frames, cap, T=5):
     cat = np.concatenate(frames, axis=0)
     offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
