@@ -127,7 +127,7 @@ struct bvx_handle {
     std::vector<SegDesc> h_segs;
     std::vector<char> uploaded;  // byte image of the last uploaded layout
     bool all_plain = false;      // every frame of the current layout is one plain segment
-    static const int kRing = 16;   // >= sub-batches of a pipelined host call, so enqueueing them never waits for the device
+    static const int kRing = 32;   // >= sub-batches of a pipelined host call, so enqueueing them never waits for the device
     char* pin[kRing] = {};
     cudaEvent_t pin_ev[kRing];
     size_t pin_bytes = 0;
@@ -148,6 +148,11 @@ struct bvx_handle {
     int32_t* pin_idx = nullptr;        // pinned mirror of dev_idx
     size_t pin_idx_count = 0;
     std::vector<cudaEvent_t> ev_out;   // per sub-batch: its D2H copies have landed
+    float* pin_rows = nullptr;         // pinned: compact kept rows of the host form (specialised gather)
+    size_t pin_rows_floats = 0;
+    int* dev_tile_base = nullptr;      // [frames, tiles] start of each gather tile's rows
+    int32_t* pin_tile_base = nullptr;
+    size_t tile_base_count = 0;
     float cut_ratio = 0.f;             // largest (cut-off index / points) over the frames of the last call; 0 = unknown
     unsigned long long last_h2d = 0, last_d2h = 0;   // bytes moved by the last host-form call
     int last_redo = 0;                 // sub-batches of the last call that had to be redone with full frames
@@ -292,6 +297,9 @@ extern "C" int bvx_destroy(bvx_handle* h)
     delete h->pool;
     cudaFree(h->dev_idx);
     if (h->pin_idx) cudaFreeHost(h->pin_idx);
+    cudaFree(h->dev_tile_base);
+    if (h->pin_tile_base) cudaFreeHost(h->pin_tile_base);
+    if (h->pin_rows) cudaFreeHost(h->pin_rows);
     if (h->pin_offs) cudaFreeHost(h->pin_offs);
     if (h->pin_state) cudaFreeHost(h->pin_state);
     if (h->stage_in) cudaFreeHost(h->stage_in);
@@ -546,6 +554,8 @@ struct Outputs {
     int coor_cols;
     int frame_base;
     int32_t* idx = nullptr;        // optional [sum M, T] point indices (host form); voxels may then be null
+    float* crow = nullptr;         // optional compact kept rows + per-tile bases (host form, specialised gather)
+    int* tile_base = nullptr;
 };
 
 // Pipeline kernels are launched with programmatic stream serialization (see pdl_prologue()).
@@ -579,7 +589,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     const int cap = max_voxels > 0 ? max_voxels : h->cfg.max_voxels;
     if (cap > h->cfg.max_voxels)
         return fail(h, BVX_ERR_WORKSPACE, "max_voxels=%d exceeds the handle capacity %d", cap, h->cfg.max_voxels);
-    if ((!o.voxels && !o.idx) || !o.coors || !o.num_points)
+    if ((!o.voxels && !o.idx && !o.crow) || !o.coors || !o.num_points)
         return fail(h, BVX_ERR_BAD_ARGUMENT, "null output pointer");
     if (((uintptr_t)o.voxels & 15) || ((uintptr_t)o.coors & 15))
         return fail(h, BVX_ERR_BAD_ARGUMENT, "voxels/coors must be 16-byte aligned");
@@ -623,6 +633,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.clear_rows = 0;
     p.voxels = o.voxels;
     p.idx_out = o.idx;
+    p.crow = reinterpret_cast<float4*>(o.crow);
+    p.tile_base = o.tile_base;
     p.coors = o.coors;
     p.num_points = o.num_points;
     p.mean_out = o.mean;
@@ -671,6 +683,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         }
     }
     const bool small = T <= kChainMaxT && f_out == 4 && p.vec4 && h->all_plain;
+    if (o.crow && !small)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "compact rows need the specialised gather (T <= 8, 4 aligned features)");
     if (small) {
         const int tiles = (cap + kBlock - 1) / kBlock;
         const size_t smem = (size_t)kWarps * 32 * T * 16;
@@ -865,7 +879,7 @@ static int stage_out(bvx_handle* h, void* dst[3], const void* src[3], const size
 // Kernels of sub-batch k (frames [f0, f1), the first pre[f] points of each) on st, then the
 // D2H of its offsets and per-frame state into the pinned mirrors.
 static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::vector<int>& pre, int f0, int f1,
-                               int k, int fs, int f, int cap, bool assemble, cudaStream_t st)
+                               int k, int fs, int f, int cap, int mode, cudaStream_t st)
 {
     const int T = h->cfg.max_num_points;
     const int bk = f1 - f0;
@@ -878,9 +892,13 @@ static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::ve
     const size_t v0 = (size_t)f0 * cap;
     Outputs o{h->dev_voxels + v0 * T * f, h->dev_coors + v0 * 4, h->dev_num + v0,
               h->dev_offs_sub + (size_t)k * (fs + 1), nullptr, nullptr, 0, 4, f0};
-    if (assemble) {            // indices instead of rows: the host assembles the rows (assemble_rows)
+    if (mode == 1) {           // indices instead of rows: the host assembles the rows (assemble_rows)
         o.voxels = nullptr;
         o.idx = h->dev_idx + v0 * T;
+    } else if (mode == 2) {    // compact kept rows (in the sub-batch's share of the row buffer) + tile bases
+        o.crow = o.voxels;
+        o.voxels = nullptr;
+        o.tile_base = h->dev_tile_base + (size_t)f0 * ((cap + kBlock - 1) / kBlock);
     }
     int rc = run_pipeline(h, fr, f, f, cap, o, st);
     if (rc) return rc;
@@ -944,12 +962,51 @@ static void assemble_rows(bvx_handle* h, const float* points, const int32_t* off
     });
 }
 
+// Same, for the specialised gather (T <= 8, 4 features): the kept rows themselves come home,
+// compact -- 16 bytes per kept point, tile after tile of 256 voxels, voxel after voxel -- so the
+// host reads them front to back (no random access into the points) and only pads.
+static void assemble_compact(bvx_handle* h, const int32_t* fvo, int f0, int f1, int tiles, const int32_t* tile_base,
+                             const float* rows, int T, float* voxels, const int32_t* num_points)
+{
+    const int ntile = (f1 - f0) * tiles;
+    if (ntile <= 0) return;
+    h->pool->run([=](int share, int shares) {
+        const int per = (ntile + shares - 1) / shares;
+        const int lo = std::min(ntile, per * share), hi = std::min(ntile, per * (share + 1));
+        for (int j = lo; j < hi; ++j) {
+            const int i = f0 + j / tiles, t = j % tiles;
+            const size_t g0 = (size_t)fvo[i] + (size_t)t * kBlock;
+            const size_t g1 = std::min<size_t>((size_t)fvo[i + 1], g0 + kBlock);
+            if (g0 >= g1) continue;
+            const float* src = rows + (size_t)tile_base[(size_t)(i - f0) * tiles + t] * 4;
+            for (size_t gv = g0; gv < g1; ++gv) {
+                const int n = num_points[gv];
+                float* dst = voxels + gv * (size_t)T * 4;
+#if defined(__SSE2__)
+                const __m128 zero = _mm_setzero_ps();
+                for (int s = 0; s < n; ++s) _mm_stream_ps(dst + 4 * s, _mm_load_ps(src + 4 * s));
+                for (int s = n; s < T; ++s) _mm_stream_ps(dst + 4 * s, zero);
+#else
+                memcpy(dst, src, (size_t)n * 16);
+                memset(dst + (size_t)n * 4, 0, (size_t)(T - n) * 16);
+#endif
+                src += (size_t)n * 4;
+            }
+        }
+#if defined(__SSE2__)
+        _mm_sfence();
+#endif
+    });
+}
+
 static int generate_batched_pipelined(bvx_handle* h, const float* points, const int32_t* offs, int b, int f,
                                       int cap, float* voxels, int32_t* coors4, int32_t* num_points,
                                       int32_t* fvo_host, cudaStream_t st)
 {
     const int T = h->cfg.max_num_points;
-    const int nsub = std::min(b, 8);
+    // sub-batches: 8 when the rows come home by DMA; 16 with host assembly, where the first and the last
+    // sub-batch are not overlapped with anything (measured cfg4: 4 / 8 / 12 / 16 -> 3.16 / 2.71 / 2.58 / 2.52 ms)
+    const int nsub = std::min(b, h->host_assemble ? 16 : 8);
     const int fs = (b + nsub - 1) / nsub;                 // frames per sub-batch
     const int ns = (b + fs - 1) / fs;
     if (!h->s_h2d) CK(h, cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
@@ -965,6 +1022,11 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         h->ev_done.push_back(e);
     }
     const bool assemble = h->host_assemble;
+    // specialised gather (T <= 8, 4 features, 16-byte aligned rows): the kept rows come home compact;
+    // otherwise the point indices do and the rows are read from the caller's points
+    const bool compact = assemble && T <= kChainMaxT && f == 4 && ((uintptr_t)voxels & 15) == 0;
+    const int mode = compact ? 2 : (assemble ? 1 : 0);
+    const int tiles = (cap + kBlock - 1) / kBlock;
     if (assemble) {
         if (!h->pool) {
             h->pool = new HostPool();
@@ -976,7 +1038,28 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
             h->ev_out.push_back(e);
         }
         const size_t cnt = (size_t)b * cap * T;
-        if (cnt > h->pin_idx_count) {
+        if (compact) {
+            // kept rows of the call: at most one per point and at most T per voxel
+            const size_t rf = std::min((size_t)offs[b], cnt) * 4;
+            if (rf > h->pin_rows_floats) {
+                if (h->pin_rows) cudaFreeHost(h->pin_rows);
+                h->pin_rows = nullptr;
+                h->pin_rows_floats = 0;
+                CK(h, cudaMallocHost((void**)&h->pin_rows, rf * 4));
+                h->pin_rows_floats = rf;
+            }
+            const size_t tb = (size_t)b * tiles;
+            if (tb > h->tile_base_count) {
+                if (h->pin_tile_base) cudaFreeHost(h->pin_tile_base);
+                h->pin_tile_base = nullptr;
+                cudaFree(h->dev_tile_base);
+                h->dev_tile_base = nullptr;
+                h->tile_base_count = 0;
+                CK(h, cudaMallocHost((void**)&h->pin_tile_base, tb * 4));
+                CK(h, cudaMalloc((void**)&h->dev_tile_base, tb * 4));
+                h->tile_base_count = tb;
+            }
+        } else if (cnt > h->pin_idx_count) {
             if (h->pin_idx) cudaFreeHost(h->pin_idx);
             h->pin_idx = nullptr;
             cudaFree(h->dev_idx);
@@ -1042,12 +1125,11 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
     }
     // (Letting the DMA engine bring the rows of every second / third / fourth sub-batch while the threads
     // assemble the others measured slower than assembling all of them: 3.5 / 3.0 / 2.85 vs 2.87 ms.)
-    const std::vector<char> asm_k(ns, assemble ? 1 : 0);
     // leg 2: the kernels of each sub-batch on the caller's stream, outputs at capacity stride
     for (int k = 0; k < ns; ++k) {
         const int f0 = k * fs, f1 = std::min(b, f0 + fs);
         CK(h, cudaStreamWaitEvent(st, h->ev_h2d[k], 0));
-        int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, asm_k[k] != 0, st);
+        int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, mode, st);
         if (rc) return rc;
         CK(h, cudaEventRecord(h->ev_done[k], st));
     }
@@ -1058,9 +1140,22 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         return std::chrono::duration<double, std::micro>(b - a).count(); };
     double t_done = 0, t_out = 0, t_asm = 0;
     const auto t_leg3 = now();
-    std::vector<size_t> sub_run(ns, 0), sub_m(ns, 0);
-    int pending = -1;
-    size_t run = 0;
+    std::vector<size_t> sub_run(ns, 0), sub_m(ns, 0), sub_rows(ns, 0);
+    size_t run = 0, rows_run = 0;
+    auto assemble_sub = [&](int j) -> int {
+        { const auto a = now(); CK(h, cudaEventSynchronize(h->ev_out[j])); t_out += us(a, now()); }
+        const int g0 = j * fs, g1 = std::min(b, g0 + fs);
+        const auto a = now();
+        if (sub_m[j] == 0) return BVX_OK;
+        if (mode == 2)
+            assemble_compact(h, fvo_host, g0, g1, tiles, h->pin_tile_base + (size_t)g0 * tiles,
+                             h->pin_rows + sub_rows[j] * 4, T, voxels, num_points);
+        else
+            assemble_rows(h, points, offs, fvo_host, g0, g1, sub_run[j], sub_m[j], T, f, voxels, num_points,
+                          h->pin_idx);
+        t_asm += us(a, now());
+        return BVX_OK;
+    };
     fvo_host[0] = 0;
     for (int k = 0; k < ns; ++k) {
         const int f0 = k * fs, f1 = std::min(b, f0 + fs), bk = f1 - f0;
@@ -1079,7 +1174,7 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
                 h->last_h2d += (size_t)(n - pre[i]) * f * 4;
                 pre[i] = n;
             }
-            int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, asm_k[k] != 0, st);
+            int rc = pipelined_sub_batch(h, offs, pre, f0, f1, k, fs, f, cap, mode, st);
             if (rc) return rc;
             CK(h, cudaStreamSynchronize(st));
             h->last_redo += 1;
@@ -1087,41 +1182,44 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         const int32_t* lo = h->pin_offs + (size_t)k * (fs + 1);
         const size_t m = (size_t)lo[bk], v0 = (size_t)f0 * cap;
         for (int i = 1; i <= bk; ++i) fvo_host[f0 + i] = (int32_t)(run + (size_t)lo[i]);
+        size_t rows_k = 0;
+        if (compact)
+            for (int i = f0; i < f1; ++i) rows_k += (size_t)h->pin_state[i].rows;
         if (m > 0) {
-            if (asm_k[k])
+            if (mode == 2) {
+                CK(h, cudaMemcpyAsync(h->pin_rows + rows_run * 4, h->dev_voxels + v0 * T * f, rows_k * 16,
+                                      cudaMemcpyDeviceToHost, h->s_d2h));
+                CK(h, cudaMemcpyAsync(h->pin_tile_base + (size_t)f0 * tiles, h->dev_tile_base + (size_t)f0 * tiles,
+                                      (size_t)bk * tiles * 4, cudaMemcpyDeviceToHost, h->s_d2h));
+                h->last_d2h += rows_k * 16 + (size_t)bk * tiles * 4;
+            } else if (mode == 1) {
                 CK(h, cudaMemcpyAsync(h->pin_idx + run * T, h->dev_idx + v0 * T, m * T * 4, cudaMemcpyDeviceToHost,
                                       h->s_d2h));
-            else
+                h->last_d2h += m * (size_t)T * 4;
+            } else {
                 CK(h, cudaMemcpyAsync(voxels + run * T * f, h->dev_voxels + v0 * T * f, m * T * f * 4,
                                       cudaMemcpyDeviceToHost, h->s_d2h));
+                h->last_d2h += m * (size_t)T * f * 4;
+            }
             CK(h, cudaMemcpyAsync(coors4 + run * 4, h->dev_coors + v0 * 4, m * 16, cudaMemcpyDeviceToHost, h->s_d2h));
             CK(h, cudaMemcpyAsync(num_points + run, h->dev_num + v0, m * 4, cudaMemcpyDeviceToHost, h->s_d2h));
-            h->last_d2h += m * ((size_t)T * (asm_k[k] ? 1 : f) * 4 + 16 + 4);
+            h->last_d2h += m * (16 + 4);
         }
-        sub_run[k] = run; sub_m[k] = m;
+        sub_run[k] = run; sub_m[k] = m; sub_rows[k] = rows_run;
         if (assemble) {
-            // the sub-batch whose indices came home last is assembled while this one's copies are in flight
+            // the previous sub-batch is assembled while this one's copies are in flight
             CK(h, cudaEventRecord(h->ev_out[k], h->s_d2h));
-            if (pending >= 0) {
-                { const auto a = now(); CK(h, cudaEventSynchronize(h->ev_out[pending])); t_out += us(a, now()); }
-                const int g0 = pending * fs, g1 = std::min(b, g0 + fs);
-                const auto a = now();
-                assemble_rows(h, points, offs, fvo_host, g0, g1, sub_run[pending], sub_m[pending], T, f, voxels,
-                              num_points, h->pin_idx);
-                t_asm += us(a, now());
-                pending = -1;
+            if (k > 0) {
+                const int rc = assemble_sub(k - 1);
+                if (rc) return rc;
             }
-            if (asm_k[k]) pending = k;
         }
         run += m;
+        rows_run += rows_k;
     }
-    if (pending >= 0) {
-        { const auto a = now(); CK(h, cudaEventSynchronize(h->ev_out[pending])); t_out += us(a, now()); }
-        const int g0 = pending * fs, g1 = std::min(b, g0 + fs);
-        const auto a = now();
-        assemble_rows(h, points, offs, fvo_host, g0, g1, sub_run[pending], sub_m[pending], T, f, voxels, num_points,
-                      h->pin_idx);
-        t_asm += us(a, now());
+    if (assemble) {
+        const int rc = assemble_sub(ns - 1);
+        if (rc) return rc;
     }
     if (trace)
         fprintf(stderr, "[bvx] leg3 %.0f us: wait kernels %.0f, wait copies %.0f, assemble %.0f (%d threads)\n",

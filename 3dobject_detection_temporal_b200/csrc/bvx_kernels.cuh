@@ -81,7 +81,7 @@ struct FrameState {
     int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
     int n_done;       // points that went through k_insert (prefix), published by the scan
     int cleared;      // k_insert: table slices cleared so far (hashed grid); reset by k_slot
-    int pad_;
+    int rows;         // k_gather_small, compact-row mode: kept points of the frame (reset by the frame scan)
 };
 
 struct Pipe {
@@ -99,7 +99,7 @@ struct Pipe {
     int* bucket;
     int* cnt;
     int2* ovf;
-    int* counters;       // [0] frames-done ticket, [1] overflow count
+    int* counters;       // [0] frames-done ticket, [1] overflow count, [2] compact rows handed out
     int* frame_voxel_offsets;
     int* voxel_num;      // optional [1]: total number of voxels of the call
     int nframes;
@@ -114,6 +114,10 @@ struct Pipe {
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
     int clear_rows;      // hashed tables: the first clear_rows block rows of k_insert clear the tables (0: dense grid)
     // outputs
+    float4* crow;        // optional, specialised gather only: the kept rows of the call, compact (no padding): a tile
+                         // of 256 voxels owns the range starting at tile_base[frame * tiles + tile] (ranges are
+                         // handed out in arrival order from counters[2]), voxel after voxel, slots in order
+    int* tile_base;
     int* idx_out;        // optional [sum M, T]: frame-local point index of every kept (voxel, slot), -1 = empty.
                          // With it, voxels may be null: the host form assembles the rows from its own copy
                          // of the points (the padded rows are 4-5x their information and PCIe is the bound)
@@ -480,6 +484,7 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, i
         p.state[f].total = total;
         p.state[f].m = min(total, cap);
         p.state[f].done_verify = 0;            // ready for the next call
+        p.state[f].rows = 0;
         p.state[f].n_done = eff;
         if (!cut) p.state[f].istar = eff;
     }
@@ -531,6 +536,7 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, i
         if (p.voxel_num) *p.voxel_num = carry;         // single-frame form: M for the caller
         p.counters[0] = 0;
         p.counters[1] = 0;
+        p.counters[2] = 0;
     }
 }
 
@@ -839,6 +845,24 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
             if ((T & 1) == 0) q ^= (q >> 3) & 7;
             if (j < wn * T) __stcs(out + j, sw[q]);
         }
+    }
+    if (p.crow) {
+        // compact rows for the host form: the tile reserves a range for its kept points, each voxel
+        // writes its rows (slots 0 .. nvalid-1 of the sorted bucket) at its prefix inside the range
+        __shared__ int s_scan[kWarps + 1];
+        __shared__ int s_base;
+        int tot;
+        const int ex = block_exclusive_scan(nvalid, &tot, s_scan);
+        if (threadIdx.x == 0) {
+            s_base = atomicAdd(&p.counters[2], tot);
+            p.tile_base[f * tiles + blockIdx.x] = s_base;
+            atomicAdd(&p.state[f].rows, tot);
+        }
+        __syncthreads();
+        float4* dst = p.crow + s_base + ex;
+#pragma unroll
+        for (int s = 0; s < T; ++s)
+            if (s < nvalid) __stcs(dst + s, row[s]);
     }
     if (!live) return;
     const size_t gv = gbase + v;

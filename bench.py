@@ -352,8 +352,8 @@ def run_ours(args):
                            "buffers" + ("; break mode uploads only the prefix of each frame the cut-off can reach "
                                         "(sized from the previous call, verified per frame, redone if short)"
                                         if prefix_upload and args.overflow == "break" else "; whole frames uploaded")
-                           + ("; point indices come home (4*T bytes per voxel), the padded rows are assembled from "
-                              "the caller's points by the handle's host threads" if host_assemble else
+                           + ("; the kept rows come home compact (16 bytes per kept point), the zero padding is "
+                              "written by the handle's host threads" if host_assemble else
                               "; padded rows gathered on the device and copied home"),
                     "host_threads": min(32, os.cpu_count() or 1) if host_assemble else 0,
                     "host_numa_binding": numa}

@@ -205,14 +205,17 @@ int bvx_host_free(void* p);
 int bvx_set_prefix_upload(bvx_handle* h, int32_t on);
 /* Pinned batched host form: the padded rows voxels[M, T, f] are 4-5x their
  * information (cfg4: 1.2 points per voxel in T = 5 slots) and the PCIe link is
- * what bounds the call.  With host assembly on (default) only the frame-local
- * point index of every kept (voxel, slot) comes home -- 4*T bytes per voxel
- * instead of 4*T*f -- and the rows are copied from the caller's own points,
- * zero padded, by a pool of host threads owned by the handle, sub-batch k-1
- * while the copies of sub-batch k are in flight.  Every row of the reference's
- * voxels is a verbatim copy of an input row, so the result is bit-identical;
- * voxel numbering, slots, counts and coordinates are still computed on the
- * device.  Off: the rows are gathered on the device and copied home. */
+ * what bounds the call.  With host assembly on (default) the padding does not
+ * cross the link: for T <= 8 and 4 features the kept rows come home compact
+ * (16 bytes per kept point, in voxel order, plus one int per 256 voxels), else
+ * the frame-local point index of every kept (voxel, slot) does (4*T bytes per
+ * voxel) and the rows are read from the caller's own points.  A pool of host
+ * threads owned by the handle (one per host core, at most 32) writes the padded
+ * rows with streaming stores, sub-batch k-1 while the copies of sub-batch k are
+ * in flight.  Every row of the reference's voxels is a verbatim copy of an
+ * input row, so the result is bit-identical; voxel numbering, slots, counts and
+ * coordinates are still computed on the device.  Off: the padded rows are
+ * gathered on the device and copied home. */
 int bvx_set_host_assemble(bvx_handle* h, int32_t on);
 int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes,
                       uint64_t* d2h_bytes, int32_t* redone);

@@ -354,7 +354,13 @@ def test_host_assembly_matches_device_rows(pkg, oracle, synth, T, f, assemble):
             _eq((hv, hc, hn), (wv, wc, wn), f"host assembly={assemble} T={T} f={f} {overflow} rep {rep}")
         h2d, d2h, _ = g.last_transfer()
         m = int(woff[-1])
-        assert d2h < m * (T * (4 if assemble else 4 * f) + 20) + 4096
+        if not assemble:
+            bound = m * (T * 4 * f + 20)
+        elif T <= 8 and f == 4:              # compact kept rows + one int per gather tile
+            bound = int(wn.sum()) * 16 + m * 20 + b * ((cap + 255) // 256) * 4
+        else:                                # point indices
+            bound = m * (T * 4 + 20)
+        assert d2h <= bound + 4096, (d2h, bound)
         g.close()
 
 

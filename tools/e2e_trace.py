@@ -11,8 +11,7 @@ host = np.concatenate(frames, axis=0)
 hp = pkg.pinned_empty(host.shape, np.float32); hp[:] = host
 hout = (pkg.pinned_empty((B * cap, T, F), np.float32), pkg.pinned_empty((B * cap, 4), np.int32),
         pkg.pinned_empty((B * cap,), np.int32), pkg.pinned_empty((B + 1,), np.int32))
-for asm, mod in ((True, 1), (False, 1)):
-    os.environ["BVX_ASM_MOD"] = str(mod)
+for asm, mod in ((True, 0), (False, 0)):
     g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, host_assemble=asm)
     for _ in range(3):
         g.generate_batched(hp, offs, out=hout)
@@ -20,6 +19,6 @@ for asm, mod in ((True, 1), (False, 1)):
     t0 = time.perf_counter()
     for _ in range(3):
         g.generate_batched(hp, offs, out=hout)
-    print(f"assemble={asm} mod={mod}: {(time.perf_counter() - t0) / 3 * 1e3:.3f} ms/call", flush=True)
+    print(f"assemble={asm}: {(time.perf_counter() - t0) / 3 * 1e3:.3f} ms/call", flush=True)
     os.environ.pop("BVX_TRACE")
     g.close()
