@@ -21,6 +21,7 @@
 #include <emmintrin.h>
 #include <xmmintrin.h>
 #endif
+#include <sched.h>
 #include <chrono>
 #include <condition_variable>
 #include <functional>
@@ -144,6 +145,7 @@ struct bvx_handle {
     bool prefix_upload = true;         // break mode: upload only the prefix of a frame the cut-off can reach
     bool host_assemble = true;         // pipelined host form: bring home point indices, assemble the padded rows on the host
     HostPool* pool = nullptr;          // host threads of the row assembly (created on first use)
+    int host_threads = 0;              // 0: one per core this process may run on (at most 32)
     int* dev_idx = nullptr;            // [voxel capacity, T] point index per (voxel, slot) of the host form
     int32_t* pin_idx = nullptr;        // pinned mirror of dev_idx
     size_t pin_idx_count = 0;
@@ -1030,7 +1032,15 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
     if (assemble) {
         if (!h->pool) {
             h->pool = new HostPool();
-            h->pool->start((int)std::min(32u, std::max(1u, std::thread::hardware_concurrency())));
+            int nt = h->host_threads;
+            if (nt <= 0) {
+                // the cores this process may run on (a rank bound to its GPU's NUMA node sees only those)
+                cpu_set_t set;
+                CPU_ZERO(&set);
+                nt = sched_getaffinity(0, sizeof set, &set) == 0 ? CPU_COUNT(&set)
+                                                                  : (int)std::thread::hardware_concurrency();
+            }
+            h->pool->start(std::min(32, std::max(1, nt)));
         }
         while ((int)h->ev_out.size() < ns) {
             cudaEvent_t e;
@@ -1311,6 +1321,15 @@ extern "C" int bvx_set_host_assemble(bvx_handle* h, int32_t on)
 {
     if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
     h->host_assemble = on != 0;
+    return BVX_OK;
+}
+
+extern "C" int bvx_set_host_threads(bvx_handle* h, int32_t n)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (n < 0) return fail(h, BVX_ERR_BAD_ARGUMENT, "host threads must be >= 0");
+    if (h->pool && n != h->host_threads) { delete h->pool; h->pool = nullptr; }
+    h->host_threads = n;
     return BVX_OK;
 }
 

@@ -34,7 +34,8 @@ def _is_torch(x):
 
 class VoxelGenerator:
     def __init__(self, voxel_size, point_cloud_range, max_num_points, max_voxels=20000,
-                 overflow="break", grid="hashed", device=None, prefix_upload=True, host_assemble=True):
+                 overflow="break", grid="hashed", device=None, prefix_upload=True, host_assemble=True,
+                 host_threads=None):
         if overflow not in _lib.OVERFLOW:
             raise ValueError(f"overflow must be 'break' or 'continue', got {overflow!r}")
         if grid not in _lib.GRID:
@@ -50,6 +51,12 @@ class VoxelGenerator:
         self._device = device
         self._prefix_upload = bool(prefix_upload)
         self._host_assemble = bool(host_assemble)
+        if host_threads is None:
+            # several ranks on one host (torchrun): each takes its share of the cores
+            import os
+            ranks = int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1)
+            host_threads = max(1, (os.cpu_count() or 1) // ranks) if ranks > 1 else 0
+        self._host_threads = int(host_threads)
         lib = _lib.load()
         gs = (ctypes.c_int64 * 3)()
         _lib.check(lib.bvx_grid_size(
@@ -126,6 +133,8 @@ class VoxelGenerator:
             _lib.check(_lib.load().bvx_set_prefix_upload(h, 0), h)
         if not self._host_assemble:
             _lib.check(_lib.load().bvx_set_host_assemble(h, 0), h)
+        if self._host_threads:
+            _lib.check(_lib.load().bvx_set_host_threads(h, self._host_threads), h)
         self._handle = h
         self._cap = cap
         return h

@@ -329,6 +329,7 @@ def run_ours(args):
         def host_arm(prefix_upload, host_assemble=True):
             gen_h = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=args.overflow,
                                        device=dev, prefix_upload=prefix_upload, host_assemble=host_assemble)
+            gen_threads = gen_h._host_threads or min(32, len(os.sched_getaffinity(0)))
             for _ in range(3):
                 r = gen_h.generate_batched(hp, offs, out=hout)
             if world > 1:
@@ -355,7 +356,7 @@ def run_ours(args):
                            + ("; the kept rows come home compact (16 bytes per kept point), the zero padding is "
                               "written by the handle's host threads" if host_assemble else
                               "; padded rows gathered on the device and copied home"),
-                    "host_threads": min(32, os.cpu_count() or 1) if host_assemble else 0,
+                    "host_threads": (gen_threads if host_assemble else 0),
                     "host_numa_binding": numa}
 
         e2e = host_arm(True)

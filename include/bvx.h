@@ -217,6 +217,10 @@ int bvx_set_prefix_upload(bvx_handle* h, int32_t on);
  * coordinates are still computed on the device.  Off: the padded rows are
  * gathered on the device and copied home. */
 int bvx_set_host_assemble(bvx_handle* h, int32_t on);
+/* Host threads of the assembly: 0 (default) = one per core the process may run
+ * on (sched_getaffinity), at most 32.  With several ranks per host give each
+ * its share (cores / ranks on the host). */
+int bvx_set_host_threads(bvx_handle* h, int32_t n);
 int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes,
                       uint64_t* d2h_bytes, int32_t* redone);
 
