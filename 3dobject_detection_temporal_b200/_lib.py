@@ -8,7 +8,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbvx.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 BVX_OK = 0
 BVX_ERR_BAD_ARGUMENT = 1
@@ -45,6 +45,7 @@ class BvxSweep(ctypes.Structure):
         ("R", ctypes.c_float * 9),
         ("t", ctypes.c_float * 3),
         ("dt", ctypes.c_float),
+        ("perm", ctypes.c_void_p),
     ]
 
 

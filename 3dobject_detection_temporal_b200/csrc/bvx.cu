@@ -448,6 +448,7 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
             SegDesc sd;
             memset(&sd, 0, sizeof sd);
             sd.pts = sw.points;
+            sd.perm = sw.perm;
             sd.n = sw.n;
             sd.start = (int)n;
             sd.has_transform = sw.has_transform ? 1 : 0;
@@ -474,7 +475,7 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
         if (n > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
         fd.n = (int)n;
         fd.pts0 = nullptr;
-        if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform &&
+        if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform && !frames[f].sweeps[0].perm &&
             !(frames[f].crop && frames[f].crop->n_planes > 0))
             fd.pts0 = frames[f].sweeps[0].points;
         else if (n > 0)

@@ -59,6 +59,7 @@ struct FrameDesc {
 
 struct SegDesc {
     const float* pts;
+    const int* perm;    // optional: row j of the segment is pts[perm[j]] (shuffle fused into the load)
     int n;
     int start;          // first frame-local point index of the segment
     int has_transform;
@@ -208,7 +209,8 @@ __device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int
         return;
     }
     const SegDesc& sg = find_seg(p, fr, i);
-    const float* q = sg.pts + (size_t)(i - sg.start) * p.f_in;
+    const int j = sg.perm ? __ldg(sg.perm + (i - sg.start)) : i - sg.start;
+    const float* q = sg.pts + (size_t)j * p.f_in;
     if (p.vec4) {
         const float4 v = __ldcs(reinterpret_cast<const float4*>(q));
         x = v.x; y = v.y; z = v.z;
@@ -228,7 +230,8 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
         q = fr.pts0 + (size_t)i * p.f_in;
     } else {
         sg = &find_seg(p, fr, i);
-        q = sg->pts + (size_t)(i - sg->start) * p.f_in;
+        const int j = sg->perm ? __ldg(sg->perm + (i - sg->start)) : i - sg->start;
+        q = sg->pts + (size_t)j * p.f_in;
     }
     float x, y, z;
     if (p.vec4) {

@@ -268,7 +268,9 @@ class VoxelGenerator:
         """Fill arr[base:base+len(sweeps)]; returns (f_in, points in these sweeps)."""
         import torch
         total = 0
-        for i, (pts, R, t, dt) in enumerate(sweeps):
+        for i, sw in enumerate(sweeps):
+            pts, R, t, dt = sw[:4]
+            perm = sw[4] if len(sw) > 4 else None
             if use_torch:
                 p = pts.contiguous()
                 if p.dtype != torch.float32 or not p.is_cuda:
@@ -291,11 +293,20 @@ class VoxelGenerator:
             a.R[:] = Rm.reshape(-1).tolist()
             a.t[:] = tv.tolist()
             a.dt = float(np.float32(dt))
+            a.perm = None
+            if perm is not None:
+                # the reference's shuffle_points as a gather on the load: row j = points[perm[j]]
+                q = perm if _is_torch(perm) else torch.from_numpy(np.ascontiguousarray(perm))
+                q = q.to(device=p.device, dtype=torch.int32).contiguous()
+                if q.dim() != 1 or q.shape[0] != p.shape[0]:
+                    raise ValueError("perm must be a permutation of the sweep's rows")
+                keep.append(q)
+                a.perm = q.data_ptr()
             total += int(p.shape[0])
         return f_in, total
 
     def generate_batched_sweeps(self, frames, max_voxels=None, append_dt=True, mean_channels=0, crops=None):
-        """B frames, each a list of sweeps ``(points[N_s, F_in], R or None, t or None, dt)``, key frame
+        """B frames, each a list of sweeps ``(points[N_s, F_in], R or None, t or None, dt[, perm])``, key frame
         first: the batched form of ``generate_sweeps``.  ``append_dt=False`` keeps F_out = F_in; with
         one transformed sweep per frame that is the reference's global rotation / scaling / flip
         (second/core/preprocess.py:756-804) applied in registers while the points are loaded.

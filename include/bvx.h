@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BVX_ABI_VERSION 1
+#define BVX_ABI_VERSION 2
 
 typedef enum bvx_status {
     BVX_OK = 0,
@@ -82,6 +82,10 @@ typedef struct bvx_sweep {
     float R[9];            /* row-major 3x3, sweep -> key frame */
     float t[3];
     float dt;              /* seconds, appended as channel f_in */
+    const int32_t* perm;   /* optional, device, [n]: row j of the sweep is points[perm[j]] -- the reference's
+                            * shuffle_points (np.random.shuffle before voxelization; input_reader.proto:10,
+                            * second/configs/.../server_lidaronly.fhd.onestage.config:109) as a gather on the
+                            * point load instead of a shuffled copy.  NULL = rows in memory order. */
 } bvx_sweep;
 
 /* Optional convex crop of a frame's points, tested on the raw coordinates before

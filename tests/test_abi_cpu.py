@@ -19,12 +19,12 @@ def test_library_exports_every_declared_symbol(pkg):
     lib = ctypes.CDLL(pkg._lib.LIB_PATH)
     for name in declared:
         assert hasattr(lib, name), name
-    assert pkg._lib.load().bvx_abi_version() == 1
+    assert pkg._lib.load().bvx_abi_version() == 2
 
 
 def test_struct_layouts_match_header(pkg):
     assert ctypes.sizeof(pkg._lib.BvxConfig) == 4 * (3 + 6 + 8)
-    assert ctypes.sizeof(pkg._lib.BvxSweep) == 8 + 4 + 4 + 4 * 13 + 4   # padded to 8
+    assert ctypes.sizeof(pkg._lib.BvxSweep) == 8 + 4 + 4 + 4 * 13 + 4 + 8   # dt padded to 8, then perm
 
 
 def test_constructor_surface_matches_reference(pkg):

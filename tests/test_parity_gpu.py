@@ -214,6 +214,43 @@ def test_batched_sweeps(pkg, oracle, synth, overflow):
         _eq((hv, hc, hn), (wv, wc, wn), "batched sweeps, numpy")
 
 
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_shuffle_fused_into_the_load(pkg, oracle, synth, overflow):
+    """The reference's shuffle_points (np.random.shuffle(points) before voxelization) as a permutation
+    gathered on the point load: voxelizing (points, perm) must equal the oracle on points[perm] --
+    plain frames, a frame that is also scaled, temporal sweeps with dt, T <= 8 and long buckets."""
+    rng = np.random.default_rng(77)
+    raw = [synth.lidar_frame(n, "kitti", seed=40 + i, shuffle=False) for i, n in enumerate([15000, 0, 7000, 1])]
+    perms = [rng.permutation(p.shape[0]).astype(np.int32) for p in raw]
+    S = np.eye(3, dtype=np.float32) * np.float32(0.95)
+    xf = [(None, None), (None, None), (S, None), (None, None)]
+    for T, cap in ((5, 1200), (20, 1200)):
+        g, o = _pair(pkg, oracle, KITTI, T, cap, overflow)
+        shuffled = [np.ascontiguousarray(p[q]) for p, q in zip(raw, perms)]
+        merged = [np.ascontiguousarray(oracle.merge_sweeps([(p, R, t, 0.0)])[:, :4]) for p, (R, t) in zip(shuffled, xf)]
+        want = o.generate_batched(merged)
+        frames = [[(torch.from_numpy(p).cuda(), R, t, 0.0, torch.from_numpy(q).cuda())]
+                  for p, q, (R, t) in zip(raw, perms, xf)]
+        for _ in range(2):
+            gv, gc, gn, goff = g.generate_batched_sweeps(frames, append_dt=False)
+            assert np.array_equal(goff.cpu().numpy(), want[3])
+            _eq((gv, gc, gn), want[:3], f"shuffle T={T}")
+        hv, hc, hn, hoff = g.generate_batched_sweeps(
+            [[(p, R, t, 0.0, q)] for p, q, (R, t) in zip(raw, perms, xf)], append_dt=False)   # numpy form
+        _eq((hv, hc, hn), want[:3], f"shuffle numpy T={T}")
+    # temporal: two shuffled sweeps with dt, single-frame form
+    g, o = _pair(pkg, oracle, KITTI, 5, 2000, overflow)
+    a, b = raw[0], raw[2]
+    qa, qb = perms[0], perms[2]
+    R, t = _rot_z(0.01), np.asarray([0.3, 0.0, 0.0], np.float32)
+    wv, wc, wn = o.generate(oracle.merge_sweeps([(a[qa], None, None, 0.0), (b[qb], R, t, 0.1)]))
+    gv, gc, gn = g.generate_sweeps([(torch.from_numpy(a).cuda(), None, None, 0.0, torch.from_numpy(qa).cuda()),
+                                    (torch.from_numpy(b).cuda(), R, t, 0.1, torch.from_numpy(qb).cuda())])
+    _eq((gv, gc, gn), (wv, wc, wn), "shuffled sweeps")
+    with pytest.raises(ValueError):
+        g.generate_sweeps([(a, None, None, 0.0, qa[:-1])])
+
+
 def test_global_augmentation_fused_into_the_load(pkg, oracle, synth):
     """One transformed sweep per frame, no dt channel: the reference's global rotation / scaling / flip
     (second/core/preprocess.py:756-804) applied while the points are loaded.  Voxels are bit-exact
