@@ -640,6 +640,43 @@ def test_pillar_pipeline_to_canvas(pkg, oracle, synth):
     assert torch.all(feat2.grad == 1)
 
 
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_cuda_graph_replay(pkg, oracle, synth, overflow):
+    """The device forms enqueue only kernels (no host sync, no allocation of their own), so a call can
+    be captured into a CUDA graph -- programmatic-dependent-launch edges included -- and replayed on
+    new data in the same buffers: single frame (padded form) and a batch with the fused mean VFE."""
+    g, o = _pair(pkg, oracle, KITTI, 5, 2500, overflow)
+    frames = [synth.lidar_frame(20000, "kitti", seed=500 + i) for i in range(4)]
+    buf = torch.empty((20000, 4), dtype=torch.float32, device="cuda")
+    buf.copy_(torch.from_numpy(frames[0]))
+    graph, (v, c, n, cnt) = g.capture(buf)
+    for f in frames[1:] + frames[:1]:
+        buf.copy_(torch.from_numpy(f))
+        graph.replay()
+        torch.cuda.synchronize()
+        m = int(cnt.item())
+        _eq((v[:m], c[:m], n[:m]), o.generate(f), "graph replay, single frame")
+    # batched, out= buffers, fused mean
+    cat = torch.empty((3 * 20000, 4), dtype=torch.float32, device="cuda")
+    offs = np.asarray([0, 20000, 40000, 60000], np.int32)
+    cat.copy_(torch.from_numpy(np.concatenate(frames[:3])))
+    out = g.generate_batched(cat, offs, mean_channels=4, padded=True)
+    torch.cuda.synchronize()
+    graph2 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph2):
+        g.generate_batched(cat, offs, mean_channels=4, padded=True, out=out)
+    for order in ([1, 2, 3], [3, 0, 2]):
+        fr = [frames[i] for i in order]
+        cat.copy_(torch.from_numpy(np.concatenate(fr)))
+        graph2.replay()
+        torch.cuda.synchronize()
+        wv, wc, wn, woff = o.generate_batched(fr)
+        assert np.array_equal(out[3].cpu().numpy(), woff)
+        m = int(woff[-1])
+        _eq((out[0][:m], out[1][:m], out[2][:m]), (wv, wc, wn), "graph replay, batch")
+        np.testing.assert_allclose(out[4][:m].cpu().numpy(), oracle.mean_vfe(wv, wn), rtol=1e-6, atol=0)
+
+
 def test_errors(pkg):
     g = pkg.VoxelGenerator([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 100)
     with pytest.raises(ValueError):

@@ -35,8 +35,24 @@ for name in names:
         call()
     torch.cuda.synchronize()
     pr = gen.profile_read()
+    # the same call as a CUDA graph replay (padded single-frame form only): no Python / launch overhead
+    graph_us = None
+    if c["sweeps"] == 1:
+        gcall = lambda: gen.generate_padded(pts)
+        gcall(); torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            gcall()
+        tg = []
+        for _ in range(20):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); graph.replay(); e1.record(); torch.cuda.synchronize()
+            tg.append(e0.elapsed_time(e1))
+        graph_us = float(np.median(tg)) * 1e3
     alg = 4 * n * 4 + m * (T * f_out * 4 + 12 + 4)
     print(f"{name}: points={n} voxels={m} kept={kept} T={T} call={ms*1e3:.1f}us -> {n/ms/1e3:.0f} Mpoints/s, "
-          f"algorithmic {alg/1e6:.1f} MB -> {alg/ms/1e6:.0f} GB/s | " +
+          f"algorithmic {alg/1e6:.1f} MB -> {alg/ms/1e6:.0f} GB/s" +
+          (f", graph replay {graph_us:.1f}us" if graph_us else "") + " | " +
           " ".join(f"{k}={v[0]/v[1]*1e3:.1f}" for k, v in pr.items() if v[1]))
     gen.close()
