@@ -88,6 +88,7 @@ SYMBOLS = {
                                          ctypes.POINTER(_i32)]),
     "bvx_mean_vfe": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_scatter_bev": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "bvx_scatter_bev_dev": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_anchors_area_workspace_bytes": (ctypes.c_size_t, [_i32, _i32, _i32, _i32, _i32]),
     "bvx_anchors_area": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(ctypes.c_float),
                                         ctypes.POINTER(ctypes.c_float), ctypes.POINTER(_i32), _i32, _vp, _i32,

@@ -592,7 +592,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     const int cap = max_voxels > 0 ? max_voxels : h->cfg.max_voxels;
     if (cap > h->cfg.max_voxels)
         return fail(h, BVX_ERR_WORKSPACE, "max_voxels=%d exceeds the handle capacity %d", cap, h->cfg.max_voxels);
-    if ((!o.voxels && !o.idx && !o.crow) || !o.coors || !o.num_points)
+    if ((!o.voxels && !o.idx && !o.crow && !o.mean) || !o.coors || !o.num_points)
         return fail(h, BVX_ERR_BAD_ARGUMENT, "null output pointer");
     if (((uintptr_t)o.voxels & 15) || ((uintptr_t)o.coors & 15))
         return fail(h, BVX_ERR_BAD_ARGUMENT, "voxels/coors must be 16-byte aligned");
@@ -1395,8 +1395,25 @@ extern "C" int bvx_mean_vfe(const float* voxels, const int32_t* num_points, int3
     return BVX_OK;
 }
 
+static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, const int32_t* m_dev, int32_t c,
+                       int32_t b, int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream);
+
 extern "C" int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m, int32_t c, int32_t b,
                                int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream)
+{
+    return scatter_bev(feats, coors4, m, nullptr, c, b, d, ny, nx, canvas, stream);
+}
+
+extern "C" int bvx_scatter_bev_dev(const float* feats, const int32_t* coors4, const int32_t* m_dev, int32_t m_cap,
+                                   int32_t c, int32_t b, int32_t d, int32_t ny, int32_t nx, float* canvas,
+                                   void* stream)
+{
+    if (!m_dev) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null voxel count pointer");
+    return scatter_bev(feats, coors4, m_cap, m_dev, c, b, d, ny, nx, canvas, stream);
+}
+
+static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, const int32_t* m_dev, int32_t c,
+                       int32_t b, int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream)
 {
     if (m < 0 || c < 1 || b < 1 || d < 1 || ny < 1 || nx < 1)
         return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad scatter shape");
@@ -1413,7 +1430,7 @@ extern "C" int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_
     if (m > 0) {
         const long long work = (long long)m * c;
         k_scatter<<<(unsigned)((work + kBlock - 1) / kBlock), kBlock, 0, st>>>(
-            feats, reinterpret_cast<const int4*>(coors4), m, c, b, d, ny, nx, canvas);
+            feats, reinterpret_cast<const int4*>(coors4), m, c, b, d, ny, nx, canvas, m_dev);
         g_launches += 1;
     }
     cudaError_t e = cudaGetLastError();

@@ -1038,12 +1038,15 @@ __global__ void __launch_bounds__(kBlock) k_fill_zero(float4* __restrict__ p, si
 }
 
 // one thread per (voxel, channel): canvas[b, c*D + z, y, x] = feats[i, c]
+// m_dev (optional): the number of voxels lives on the device (frame_voxel_offsets[B] of the call that
+// produced them); m is then the capacity the launch was sized for.
 __global__ void __launch_bounds__(kBlock) k_scatter(const float* __restrict__ feats,
                                                     const int4* __restrict__ coors, int m, int c,
                                                     int b, int d, int ny, int nx,
-                                                    float* __restrict__ canvas)
+                                                    float* __restrict__ canvas, const int* __restrict__ m_dev)
 {
     const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    if (m_dev) m = min(m, __ldg(m_dev));
     if (t >= (long long)m * c) return;
     const int i = (int)(t / c), ch = (int)(t - (long long)i * c);
     const int4 q = __ldg(coors + i);

@@ -382,6 +382,52 @@ class VoxelGenerator:
         return out
 
     # ---- B frames per call (+ the voxel part of merge_second_batch)
+    def generate_bev(self, points, frame_offsets, max_voxels=None, channels=4, out=None):
+        """Fused pillar path, points -> BEV canvas, device tensors only and no host sync: voxelization
+        with the mean VFE fused into the gather (the padded ``[M, T, F]`` rows are never written) and the
+        PointPillars scatter of ``middle.py:513-526`` reading the voxel count from the device.  Equals
+        ``PointPillarsScatter(...)(VoxelFeatureExtractorV3()(voxels, num), coors, B)`` on the outputs of
+        ``generate_batched``.  Returns ``(canvas [B, C*D, H, W], voxel_features [cap, C], coors [cap, 4],
+        num_points [cap], frame_voxel_offsets [B+1])`` at capacity; ``out=`` reuses a previous return."""
+        import torch
+        max_voxels = int(max_voxels or self._max_voxels)
+        if not _is_torch(points) or not points.is_cuda or points.dtype != torch.float32 or points.dim() != 2:
+            raise ValueError("points must be a float32 CUDA [N, F] tensor")
+        points = points.contiguous()
+        n, f = points.shape
+        offs = np.ascontiguousarray(frame_offsets, dtype=np.int32)
+        b = offs.shape[0] - 1
+        if b < 1 or offs[0] != 0 or int(offs[-1]) != n:
+            raise ValueError("frame_offsets must be [B+1], start at 0 and end at the number of points")
+        c = int(channels)
+        if not 1 <= c <= f:
+            raise ValueError(f"channels must be in [1, {f}]")
+        dev = points.device
+        h = self._ensure(n, b, max_voxels, f, dev.index)
+        cap = b * max_voxels
+        gx, gy, gz = (int(x) for x in self._grid_size)
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            if out is not None:
+                canvas, feats, coors, num, fvo = out
+                if (tuple(canvas.shape) != (b, c * gz, gy, gx) or tuple(feats.shape) != (cap, c)
+                        or tuple(coors.shape) != (cap, 4) or num.shape[0] != cap or fvo.shape[0] != b + 1):
+                    raise ValueError("out= buffers do not match this call's shapes")
+            else:
+                canvas = torch.empty((b, c * gz, gy, gx), dtype=torch.float32, device=dev)
+                feats = torch.empty((cap, c), dtype=torch.float32, device=dev)
+                coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
+                num = torch.empty((cap,), dtype=torch.int32, device=dev)
+                fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(lib.bvx_generate_batched(
+                h, points.data_ptr(), offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), b, f, max_voxels,
+                None, coors.data_ptr(), num.data_ptr(), fvo.data_ptr(), feats.data_ptr(), c, st), h)
+            _lib.check(lib.bvx_scatter_bev_dev(
+                feats.data_ptr(), coors.data_ptr(), fvo.data_ptr() + 4 * b, cap, c, b, gz, gy, gx,
+                canvas.data_ptr(), st))
+        return canvas, feats, coors, num, fvo
+
     def generate_batched(self, points, frame_offsets=None, max_voxels=None, mean_channels=0,
                          padded=False, out=None):
         """Voxelize B frames in one call.

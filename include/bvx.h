@@ -150,7 +150,8 @@ int bvx_generate_sweeps(bvx_handle* h, const bvx_sweep* sweeps_host, int32_t k,
  *   num_points           [b * max_voxels]
  *   frame_voxel_offsets  [b + 1] DEVICE int32, exclusive prefix of M_b
  *   mean_features        optional [b * max_voxels, mean_channels] f32: the mean
- *                        VFE fused into the gather (NULL to skip)            */
+ *                        VFE fused into the gather (NULL to skip).  With it,
+ *                        voxels may be NULL: the padded rows are not written. */
 int bvx_generate_batched(bvx_handle* h, const float* points,
                          const int32_t* frame_offsets_host, int32_t b, int32_t f,
                          int32_t max_voxels, float* voxels, int32_t* coors4,
@@ -247,6 +248,16 @@ int bvx_mean_vfe(const float* voxels, const int32_t* num_points, int32_t m,
 int bvx_scatter_bev(const float* feats, const int32_t* coors4, int32_t m,
                     int32_t c, int32_t b, int32_t d, int32_t ny, int32_t nx,
                     float* canvas, void* stream);
+/* Same, with the number of voxels read from device memory (frame_voxel_offsets + B
+ * of the bvx_generate_batched call that produced them; m_cap = the capacity the
+ * arrays were sized for): points -> canvas without a host synchronisation.
+ * Together with bvx_generate_batched(voxels = NULL, mean_features = feats) this is
+ * the fused pillar path: the padded [M, T, f] rows are never written (SURVEY 8d:
+ * algorithmic bytes 4*(N*f + B*C*ny*nx)). */
+int bvx_scatter_bev_dev(const float* feats, const int32_t* coors4,
+                        const int32_t* m_dev, int32_t m_cap, int32_t c, int32_t b,
+                        int32_t d, int32_t ny, int32_t nx, float* canvas,
+                        void* stream);
 
 /* Anchors area from voxel coordinates, the computation
  * behind the reference's anchors_mask:

@@ -640,6 +640,38 @@ def test_pillar_pipeline_to_canvas(pkg, oracle, synth):
     assert torch.all(feat2.grad == 1)
 
 
+@pytest.mark.parametrize("name,T,cap", [("cfg3", 100, 12000), ("cfg3", 100, 700), ("coarse", 5, 3000)])
+def test_fused_points_to_canvas(pkg, oracle, synth, name, T, cap):
+    """generate_bev: voxelization + fused mean VFE + BEV scatter with the voxel count read on the device,
+    the padded rows never written.  Must equal the three separate reference steps on the oracle's voxels
+    (pillars through the general gather, SECOND-sized voxels through the specialised one, D > 1)."""
+    c = synth.CONFIGS[name] if name != "coarse" else dict(voxel_size=[0.4, 0.4, 1.0],
+                                                         point_cloud_range=[0, -40, -3, 70.4, 40, 1])
+    sizes = [50000, 0, 30000, 1]
+    frames = [synth.lidar_frame(n, "kitti", seed=120 + i) for i, n in enumerate(sizes)]
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    cat = torch.from_numpy(np.concatenate(frames)).cuda()
+    for overflow in ("break", "continue"):
+        g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=overflow)
+        o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow)
+        wv, wc, wn, woff = o.generate_batched(frames)
+        gx, gy, gz = (int(x) for x in g.grid_size)
+        out = None
+        for rep in range(2):
+            out = g.generate_bev(cat, offs, out=out)
+            canvas, feats, coors, num, fvo = out
+            torch.cuda.synchronize()
+            assert np.array_equal(fvo.cpu().numpy(), woff)
+            m = int(woff[-1])
+            assert np.array_equal(coors[:m].cpu().numpy(), wc) and np.array_equal(num[:m].cpu().numpy(), wn)
+            wf = oracle.mean_vfe(wv, wn)
+            np.testing.assert_allclose(feats[:m].cpu().numpy(), wf, rtol=1e-6, atol=0)
+            want = oracle.scatter_bev(wf, wc, len(sizes), gz, gy, gx)
+            assert canvas.shape == (len(sizes), 4 * gz, gy, gx)
+            np.testing.assert_allclose(canvas.cpu().numpy(), want, rtol=1e-6, atol=0)
+        g.close()
+
+
 @pytest.mark.parametrize("overflow", ["break", "continue"])
 def test_cuda_graph_replay(pkg, oracle, synth, overflow):
     """The device forms enqueue only kernels (no host sync, no allocation of their own), so a call can

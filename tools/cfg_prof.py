@@ -56,3 +56,24 @@ for name in names:
           (f", graph replay {graph_us:.1f}us" if graph_us else "") + " | " +
           " ".join(f"{k}={v[0]/v[1]*1e3:.1f}" for k, v in pr.items() if v[1]))
     gen.close()
+# fused pillar path (cfg3): points -> canvas in one go vs generate + mean VFE + scatter
+c = synth.CONFIGS["cfg3"]
+gen = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"])
+pts = torch.from_numpy(synth.make_frames("cfg3", 1)[0]).cuda()
+offs = np.asarray([0, pts.shape[0]], np.int32)
+vfe, gx, gy, gz = pkg.VoxelFeatureExtractorV3(), *[int(x) for x in gen.grid_size]
+sc = pkg.PointPillarsScatter([1, gz, gy, gx, 4])
+out = gen.generate_bev(pts, offs)
+def fused(): gen.generate_bev(pts, offs, out=out)
+def separate():
+    v, cc, n, off = gen.generate_batched(pts, offs)
+    sc(vfe(v, n), cc, 1)
+for nm, fn in (("fused generate_bev", fused), ("generate_batched + VFE + scatter", separate)):
+    for _ in range(5): fn()
+    torch.cuda.synchronize(); ts = []
+    for _ in range(20):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
+    print(f"cfg3 points -> canvas, {nm}: {float(np.median(ts))*1e3:.1f}us")
+
