@@ -84,6 +84,8 @@ SYMBOLS = {
     "bvx_set_prefix_upload": (ctypes.c_int, [_vp, _i32]),
     "bvx_set_host_assemble": (ctypes.c_int, [_vp, _i32]),
     "bvx_set_host_threads": (ctypes.c_int, [_vp, _i32]),
+    "bvx_host_assemble_rows": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _i32]),
+    "bvx_host_assemble_compact": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _i32]),
     "bvx_last_transfer": (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64),
                                          ctypes.POINTER(_i32)]),
     "bvx_mean_vfe": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),

@@ -923,12 +923,12 @@ static int pipelined_sub_batch(bvx_handle* h, const int32_t* offs, const std::ve
 // host threads, while the copies and kernels of the next sub-batch run.  Every row of the
 // reference's voxels is a verbatim copy of an input row, so this is bit-exact by construction.
 // Voxels [run0, run0 + m) are those of frames [f0, f1); fvo = global voxel offsets per frame.
-static void assemble_rows(bvx_handle* h, const float* points, const int32_t* offs, const int32_t* fvo, int f0, int f1,
+static void assemble_rows(HostPool* pool, const float* points, const int32_t* offs, const int32_t* fvo, int f0, int f1,
                           size_t run0, size_t m, int T, int f, float* voxels, const int32_t* num_points,
                           const int32_t* idx)
 {
     if (m == 0) return;
-    h->pool->run([=](int share, int shares) {
+    pool->run([=](int share, int shares) {
         const size_t per = (m + shares - 1) / shares;
         const size_t lo = run0 + std::min(m, per * share), hi = run0 + std::min(m, per * (share + 1));
         int fi = f0;
@@ -968,12 +968,12 @@ static void assemble_rows(bvx_handle* h, const float* points, const int32_t* off
 // Same, for the specialised gather (T <= 8, 4 features): the kept rows themselves come home,
 // compact -- 16 bytes per kept point, tile after tile of 256 voxels, voxel after voxel -- so the
 // host reads them front to back (no random access into the points) and only pads.
-static void assemble_compact(bvx_handle* h, const int32_t* fvo, int f0, int f1, int tiles, const int32_t* tile_base,
+static void assemble_compact(HostPool* pool, const int32_t* fvo, int f0, int f1, int tiles, const int32_t* tile_base,
                              const float* rows, int T, float* voxels, const int32_t* num_points)
 {
     const int ntile = (f1 - f0) * tiles;
     if (ntile <= 0) return;
-    h->pool->run([=](int share, int shares) {
+    pool->run([=](int share, int shares) {
         const int per = (ntile + shares - 1) / shares;
         const int lo = std::min(ntile, per * share), hi = std::min(ntile, per * (share + 1));
         for (int j = lo; j < hi; ++j) {
@@ -1000,6 +1000,35 @@ static void assemble_compact(bvx_handle* h, const int32_t* fvo, int f0, int f1, 
         _mm_sfence();
 #endif
     });
+}
+
+// The host half on its own (host memory only, no device needed): what the pipelined host form runs
+// per sub-batch, exported so that it can be used -- and tested -- without a GPU.
+extern "C" int bvx_host_assemble_rows(const float* points, const int32_t* frame_offsets, const int32_t* frame_voxel_offsets,
+                                      int32_t b, int32_t t, int32_t f, const int32_t* num_points, const int32_t* idx,
+                                      float* voxels, int32_t threads)
+{
+    if (b < 1 || t < 1 || f < 1 || !frame_offsets || !frame_voxel_offsets || !num_points || !idx || !voxels)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad argument");
+    HostPool pool;
+    pool.start(std::min(32, std::max(1, (int)threads)));
+    assemble_rows(&pool, points, frame_offsets, frame_voxel_offsets, 0, b, 0, (size_t)frame_voxel_offsets[b], t, f, voxels,
+                  num_points, idx);
+    return BVX_OK;
+}
+
+extern "C" int bvx_host_assemble_compact(const float* rows, const int32_t* tile_base, const int32_t* frame_voxel_offsets,
+                                         int32_t b, int32_t max_voxels, int32_t t, const int32_t* num_points,
+                                         float* voxels, int32_t threads)
+{
+    if (b < 1 || t < 1 || max_voxels < 1 || !tile_base || !frame_voxel_offsets || !num_points || !voxels ||
+        ((uintptr_t)rows & 15) || ((uintptr_t)voxels & 15))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad argument (rows and voxels must be 16-byte aligned)");
+    HostPool pool;
+    pool.start(std::min(32, std::max(1, (int)threads)));
+    assemble_compact(&pool, frame_voxel_offsets, 0, b, (max_voxels + kBlock - 1) / kBlock, tile_base, rows, t, voxels,
+                     num_points);
+    return BVX_OK;
 }
 
 static int generate_batched_pipelined(bvx_handle* h, const float* points, const int32_t* offs, int b, int f,
@@ -1159,10 +1188,10 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         const auto a = now();
         if (sub_m[j] == 0) return BVX_OK;
         if (mode == 2)
-            assemble_compact(h, fvo_host, g0, g1, tiles, h->pin_tile_base + (size_t)g0 * tiles,
+            assemble_compact(h->pool, fvo_host, g0, g1, tiles, h->pin_tile_base + (size_t)g0 * tiles,
                              h->pin_rows + sub_rows[j] * 4, T, voxels, num_points);
         else
-            assemble_rows(h, points, offs, fvo_host, g0, g1, sub_run[j], sub_m[j], T, f, voxels, num_points,
+            assemble_rows(h->pool, points, offs, fvo_host, g0, g1, sub_run[j], sub_m[j], T, f, voxels, num_points,
                           h->pin_idx);
         t_asm += us(a, now());
         return BVX_OK;

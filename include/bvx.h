@@ -226,6 +226,24 @@ int bvx_set_host_assemble(bvx_handle* h, int32_t on);
  * on (sched_getaffinity), at most 32.  With several ranks per host give each
  * its share (cores / ranks on the host). */
 int bvx_set_host_threads(bvx_handle* h, int32_t n);
+/* The host half of the assembly on its own: host memory only, no device, no
+ * handle (what the pipelined host form runs per sub-batch; also how it is
+ * tested without a GPU).
+ * rows: voxels[v, s, :] = points[frame_offsets[frame(v)] + idx[v, s], :] for
+ *   s < num_points[v], zero for the other slots; frame(v) from
+ *   frame_voxel_offsets [b + 1]; idx [M, t] frame-local point indices.
+ * compact: rows = the kept rows (4 floats each) tile after tile; tile j of
+ *   frame i (256 voxels, ceil(max_voxels / 256) tiles per frame) starts at
+ *   row tile_base[i * tiles + j]; inside a tile voxel after voxel, slot after
+ *   slot.  rows and voxels 16-byte aligned. */
+int bvx_host_assemble_rows(const float* points, const int32_t* frame_offsets,
+                           const int32_t* frame_voxel_offsets, int32_t b, int32_t t,
+                           int32_t f, const int32_t* num_points, const int32_t* idx,
+                           float* voxels, int32_t threads);
+int bvx_host_assemble_compact(const float* rows, const int32_t* tile_base,
+                              const int32_t* frame_voxel_offsets, int32_t b,
+                              int32_t max_voxels, int32_t t, const int32_t* num_points,
+                              float* voxels, int32_t threads);
 int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes,
                       uint64_t* d2h_bytes, int32_t* redone);
 
