@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbvx.so")
+# BVX_LIB: an experiment build of the same sources (tools/variants.sh); the product is libbvx.so
+LIB_PATH = os.environ.get("BVX_LIB") or os.path.join(_HERE, "libbvx.so")
 ABI_VERSION = 2
 
 BVX_OK = 0
@@ -17,7 +18,7 @@ BVX_ERR_WORKSPACE = 3
 BVX_ERR_NO_DEVICE = 4
 
 PROFILE_SLOTS = 8
-KERNEL_NAMES = ["k_insert", "k_verify", "", "k_slot", "k_overflow", "k_gather", "", ""]
+KERNEL_NAMES = ["k_insert", "k_mid", "", "", "k_overflow", "k_gather", "", ""]
 OVERFLOW = {"break": 0, "continue": 1}
 GRID = {"hashed": 0, "dense": 1}
 

@@ -106,13 +106,16 @@ struct bvx_handle {
     long long voxel_cap;   // max_frames * max_voxels
     // device workspace
     unsigned long long* table = nullptr;
-    int* slot = nullptr;
     unsigned int* cand = nullptr;
     unsigned int* lost = nullptr;
-    unsigned int* first = nullptr;
-    int* wordlocal = nullptr;
+    unsigned char* unit8 = nullptr;
+    unsigned int* chunkstat = nullptr;
+    unsigned int* lunit32 = nullptr;
+    int2* extras = nullptr;
+    int* extn = nullptr;
     int* chunkbase = nullptr;
     long long chunks_cap = 0;
+    int* vfirst = nullptr;
     int* bucket = nullptr;
     int* cnt = nullptr;
     int2* ovf = nullptr;
@@ -126,8 +129,10 @@ struct bvx_handle {
     // descriptor upload
     std::vector<FrameDesc> h_frames;
     std::vector<SegDesc> h_segs;
-    std::vector<char> uploaded;  // byte image of the last uploaded layout
+    std::vector<char> uploaded;  // byte image of the last uploaded layout (plain frames: relative to layout_base)
+    const float* layout_base = nullptr;   // plain frames of the current layout start at layout_base + FrameDesc::pts_off
     bool all_plain = false;      // every frame of the current layout is one plain segment
+    int scan_smem_chunks = kScanSmemChunks;   // frames with more chunks take the k_scan_big path (BVX_SCAN_SMEM_CHUNKS: tests)
     static const int kRing = 32;   // >= sub-batches of a pipelined host call, so enqueueing them never waits for the device
     char* pin[kRing] = {};
     cudaEvent_t pin_ev[kRing];
@@ -282,8 +287,9 @@ extern "C" int bvx_destroy(bvx_handle* h)
 {
     if (!h) return BVX_OK;
     cudaSetDevice(h->device);
-    cudaFree(h->table); cudaFree(h->slot); cudaFree(h->cand); cudaFree(h->lost); cudaFree(h->first);
-    cudaFree(h->wordlocal); cudaFree(h->chunkbase); cudaFree(h->bucket); cudaFree(h->cnt); cudaFree(h->ovf);
+    cudaFree(h->table); cudaFree(h->cand); cudaFree(h->lost); cudaFree(h->unit8); cudaFree(h->chunkstat); cudaFree(h->lunit32);
+    cudaFree(h->extras); cudaFree(h->extn); cudaFree(h->chunkbase); cudaFree(h->vfirst); cudaFree(h->bucket);
+    cudaFree(h->cnt); cudaFree(h->ovf);
     cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
     cudaFree(h->d_offsets_scratch);
     cudaFree(h->dev_points); cudaFree(h->dev_voxels); cudaFree(h->dev_coors);
@@ -344,10 +350,16 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if (!h) return fail(nullptr, BVX_ERR_CUDA, "out of host memory");
     h->cfg = *cfg;
     h->device = cfg->device;
+    if (const char* e = getenv("BVX_SCAN_SMEM_CHUNKS")) h->scan_smem_chunks = std::max(1, std::min(kScanSmemChunks, atoi(e)));
     h->ncells = ncells;
     for (int j = 0; j < 3; ++j) {
         h->grid.lo[j] = cfg->point_cloud_range[j];
         h->grid.vs[j] = cfg->voxel_size[j];
+        {
+            // reciprocal for the divide-free fast path of cell_axis(): only if it is a normal number
+            volatile float r = 1.0f / cfg->voxel_size[j];
+            h->grid.rvs[j] = std::isnormal((float)r) ? (float)r : std::nanf("");
+        }
         h->grid.gs[j] = (int)gs[j];
         h->grid.gsf[j] = (float)gs[j];
     }
@@ -360,21 +372,31 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if (e != cudaSuccess) return bail(e, "cudaSetDevice");
     const long long np = cfg->max_points, nf = cfg->max_frames;
     if (cfg->grid_kind == BVX_GRID_DENSE) h->table_slots = ncells * nf;
-    else h->table_slots = 2 * np + 1024 * nf;
-    h->words_cap = np / 32 + 2 * nf + 8;
+    else h->table_slots = 2 * (np + np / 11 + 2) + 1024 * nf;     // per frame: next power of two >= n * 12/11 + 1
+    h->words_cap = np / 32 + 6 * nf + 8;                              // per frame: rounded up to 4 words
     h->voxel_cap = (long long)cfg->max_voxels * nf;
     h->seg_cap = (int)std::max<long long>(nf, 64);
+    const long long t1 = std::max(1, cfg->max_num_points - 1);        // bucket slots per voxel (the first point lives in vfirst)
     if ((e = dalloc(h, &h->table, (size_t)h->table_slots)) != cudaSuccess) return bail(e, "alloc table");
-    if ((e = dalloc(h, &h->slot, (size_t)np)) != cudaSuccess) return bail(e, "alloc slot");
     if ((e = dalloc(h, &h->cand, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc cand");
     if ((e = dalloc(h, &h->lost, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc lost");
     if ((e = cudaMemset(h->lost, 0, (size_t)h->words_cap * 4)) != cudaSuccess) return bail(e, "memset lost");
-    if ((e = dalloc(h, &h->first, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc first");
-    if ((e = dalloc(h, &h->wordlocal, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc wordlocal");
     h->chunks_cap = np / kChunk + 2 * nf + 8;
+    if ((e = dalloc(h, &h->unit8, (size_t)h->chunks_cap * kWarps)) != cudaSuccess) return bail(e, "alloc unit8");
+    if ((e = dalloc(h, &h->chunkstat, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkstat");
+    if ((e = cudaMemset(h->chunkstat, 0, (size_t)h->chunks_cap * 4)) != cudaSuccess) return bail(e, "memset chunkstat");
+    if ((e = dalloc(h, &h->lunit32, (size_t)h->chunks_cap * 2)) != cudaSuccess) return bail(e, "alloc lunit32");
+    if ((e = cudaMemset(h->lunit32, 0, (size_t)h->chunks_cap * 8)) != cudaSuccess) return bail(e, "memset lunit32");
+    if ((e = dalloc(h, &h->extras, (size_t)h->chunks_cap * kChunk)) != cudaSuccess) return bail(e, "alloc extras");
+    if ((e = dalloc(h, &h->extn, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc extn");
     if ((e = dalloc(h, &h->chunkbase, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkbase");
-    if ((e = dalloc(h, &h->bucket, (size_t)h->voxel_cap * cfg->max_num_points)) != cudaSuccess) return bail(e, "alloc bucket");
+    if ((e = dalloc(h, &h->vfirst, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc vfirst");
+    if ((e = dalloc(h, &h->bucket, (size_t)h->voxel_cap * t1)) != cudaSuccess) return bail(e, "alloc bucket");
+    // between calls every bucket slot is empty (kEmptyIdx = 0x7F7F7F7F) and every voxel counter zero:
+    // the gather puts back what its call used
+    if ((e = cudaMemset(h->bucket, 0x7F, (size_t)h->voxel_cap * t1 * 4)) != cudaSuccess) return bail(e, "memset bucket");
     if ((e = dalloc(h, &h->cnt, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc cnt");
+    if ((e = cudaMemset(h->cnt, 0, (size_t)h->voxel_cap * 4)) != cudaSuccess) return bail(e, "memset cnt");
     if (cfg->max_num_points > kChainMaxT)
         if ((e = dalloc(h, &h->ovf, (size_t)np)) != cudaSuccess) return bail(e, "alloc ovf");
     if ((e = dalloc(h, &h->counters, 8)) != cudaSuccess) return bail(e, "alloc counters");
@@ -426,20 +448,31 @@ struct FrameSpec {
 static int insert_rows_bound(int B) { return std::max(1, (148 * 8 + B - 1) / B); }
 
 static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
-                         int* max_n_out, int* max_words_out, bool* all_aligned)
+                         int* max_n_out, bool* all_aligned)
 {
     const int B = (int)frames.size();
     h->max_tbl_lg = 0;
     h->h_frames.assign(B, FrameDesc());
     h->h_segs.clear();
-    long long pt = 0, wd = 0, tb = 0, ck = 0;
-    int max_n = 0, max_words = 0;
+    long long wd = 0, tb = 0, ck = 0, pt = 0;
+    int max_n = 0;
     bool all_plain = true;
     *all_aligned = true;
+    // Plain frames are described relative to one base pointer, which travels as a kernel argument:
+    // a new input buffer with the same frame sizes needs no descriptor upload.
+    const float* base = nullptr;
+    auto is_plain = [&](const FrameSpec& fs) {
+        return fs.k == 1 && !fs.with_dt && !fs.sweeps[0].has_transform && !fs.sweeps[0].perm &&
+               !(fs.crop && fs.crop->n_planes > 0);
+    };
+    for (int f = 0; f < B && !base; ++f)
+        if (is_plain(frames[f]) && frames[f].sweeps[0].points) base = frames[f].sweeps[0].points;
     for (int f = 0; f < B; ++f) {
         FrameDesc& fd = h->h_frames[f];
+        memset(&fd, 0, sizeof fd);
         fd.seg_begin = (int)h->h_segs.size();
         fd.seg_count = frames[f].k;
+        const bool plain = is_plain(frames[f]);
         long long n = 0;
         for (int s = 0; s < frames[f].k; ++s) {
             const bvx_sweep& sw = frames[f].sweeps[s];
@@ -447,7 +480,7 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
                 return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d sweep %d: bad points/n", f, s);
             SegDesc sd;
             memset(&sd, 0, sizeof sd);
-            sd.pts = sw.points;
+            sd.pts = plain ? nullptr : sw.points;          // a plain frame is read through base + pts_off
             sd.perm = sw.perm;
             sd.n = sw.n;
             sd.start = (int)n;
@@ -472,18 +505,20 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
             h->h_segs.push_back(sd);
             fd.seg_count = 1;
         }
-        if (n > 0x7FFFFFF0ll) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
+        if (n > (long long)kMaxFramePoints) return fail(h, BVX_ERR_BAD_ARGUMENT, "frame %d too large", f);
         fd.n = (int)n;
-        fd.pts0 = nullptr;
-        if (frames[f].k == 1 && !frames[f].with_dt && !frames[f].sweeps[0].has_transform && !frames[f].sweeps[0].perm &&
-            !(frames[f].crop && frames[f].crop->n_planes > 0))
-            fd.pts0 = frames[f].sweeps[0].points;
-        else if (n > 0)
+        fd.plain = 0;
+        fd.pts_off = 0;
+        if (plain) {
+            fd.plain = 1;
+            if (frames[f].sweeps[0].points)
+                fd.pts_off = ((long long)(intptr_t)frames[f].sweeps[0].points - (long long)(intptr_t)base) / 4;
+        } else if (n > 0) {
             all_plain = false;
+        }
         fd.chunk_off = (int)ck;
         fd.nchunks = (int)((n + kChunk - 1) / kChunk);
         ck += fd.nchunks;
-        fd.pt_off = (int)pt;
         fd.word_off = (int)wd;
         fd.nwords = (int)((n + 31) / 32);
         fd.tbl_off = (unsigned long long)tb;
@@ -492,7 +527,8 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
             fd.tbl_mask = 0xFFFFFFFFu;
             tb += h->ncells;
         } else {
-            int lg = std::max(10, ilog2_ceil((unsigned long long)n + 1));
+            // load factor <= 11/12 even when every point opens a cell of its own
+            int lg = std::max(10, ilog2_ceil((unsigned long long)n + (unsigned long long)n / 11 + 1));
             if ((1ll << lg) > h->ncells && h->ncells >= 1024) {
                 // table never needs more slots than there are cells
                 lg = std::max(10, ilog2_ceil((unsigned long long)h->ncells + 1));
@@ -503,20 +539,22 @@ static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cu
             tb += (1ll << lg);
         }
         pt += n;
-        wd += fd.nwords;
+        wd += (fd.nwords + 3) & ~3;
         max_n = std::max(max_n, fd.n);
-        max_words = std::max(max_words, fd.nwords);
     }
     if (pt > h->cfg.max_points)
         return fail(h, BVX_ERR_WORKSPACE, "%lld points exceed the handle capacity max_points=%d", pt, h->cfg.max_points);
     if (B > h->cfg.max_frames)
         return fail(h, BVX_ERR_WORKSPACE, "%d frames exceed the handle capacity max_frames=%d", B, h->cfg.max_frames);
     h->all_plain = all_plain;
+    h->layout_base = base;
     if (tb > h->table_slots || wd > h->words_cap || ck > h->chunks_cap || (int)h->h_segs.size() > h->seg_cap)
         return fail(h, BVX_ERR_WORKSPACE, "layout exceeds the workspace (table %lld/%lld, words %lld/%lld, segs %zu/%d)",
                     tb, h->table_slots, wd, h->words_cap, h->h_segs.size(), h->seg_cap);
     *max_n_out = max_n;
-    *max_words_out = max_words;
+    // Up to kInlineFrames frames travel as kernel arguments (run_pipeline copies h_frames into the
+    // Pipe); plain frames never look at the segment descriptors, so such a call uploads nothing.
+    if (B <= kInlineFrames && all_plain) return BVX_OK;
 
     const size_t fb = sizeof(FrameDesc) * (size_t)B, sb = sizeof(SegDesc) * h->h_segs.size();
     std::vector<char> img(fb + sb);
@@ -563,8 +601,8 @@ struct Outputs {
 
 // Pipeline kernels are launched with programmatic stream serialization (see pdl_prologue()).
 template <typename... KArgs, typename... Args>
-static void launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
-                     cudaStream_t st, Args... args)
+static cudaError_t launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                            cudaStream_t st, Args... args)
 {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
@@ -576,8 +614,8 @@ static void launch_k(bvx_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 bloc
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = h->pdl ? 1 : 0;
-    cudaLaunchKernelEx(&cfg, kern, args...);
     g_launches += 1;
+    return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
 static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int f_in, int f_out,
@@ -598,11 +636,36 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         return fail(h, BVX_ERR_BAD_ARGUMENT, "voxels/coors must be 16-byte aligned");
     if (o.mean && (o.mean_c < 1 || o.mean_c > f_out))
         return fail(h, BVX_ERR_BAD_ARGUMENT, "mean_channels=%d must be in [1, %d]", o.mean_c, f_out);
+    if (B > 65535) return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call");
     CK(h, cudaSetDevice(h->device));
-    int max_n = 0, max_words = 0;
+    // Everything that can fail is checked before the first launch: the kernels hand their structures
+    // from one to the next and the last one puts them back, so a call either runs whole or not at all.
+    const int T = h->cfg.max_num_points;
+    int gather_vt = 0;
+    size_t gather_smem = 0;
+    {
+        // general gather: voxels per tile ~256 bucket entries, ~1024 for long buckets (few of their entries are live)
+        int vt = std::max(1, (T > 32 ? 1024 : kBlock) / T);
+        auto tile_smem = [&](int v) {
+            return (size_t)(((v * T + 3) & ~3) + 2 * ((v + 3) & ~3)) * 4 + (size_t)v * T * f_out * 4;
+        };
+        while (vt > 1 && tile_smem(vt) > 48 * 1024) vt >>= 1;
+        gather_vt = vt;
+        gather_smem = tile_smem(vt);
+    }
+    int max_n = 0;
     bool aligned = true;
-    int rc = upload_layout(h, frames, st, &max_n, &max_words, &aligned);
+    int rc = upload_layout(h, frames, st, &max_n, &aligned);
     if (rc) return rc;
+    const bool vec4 = f_in == 4 && aligned;
+    const bool small = T <= kChainMaxT && f_out == 4 && vec4 && h->all_plain;
+    if (o.crow && !small)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "compact rows need the specialised gather (T <= 8, 4 aligned features)");
+    if (!small && gather_smem > 200 * 1024)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", gather_smem);
+    const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
+    if (chunks > 65535 - 256)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 67M points per frame");
 
     Pipe p;
     memset(&p, 0, sizeof p);
@@ -610,13 +673,17 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.frames = h->d_frames;
     p.segs = h->d_segs;
     p.state = h->d_state;
+    p.base = h->layout_base;
     p.table = h->table;
-    p.slot = h->slot;
     p.cand = h->cand;
     p.lost = h->lost;
-    p.first = h->first;
-    p.wordlocal = h->wordlocal;
+    p.unit8 = h->unit8;
+    p.chunkstat = h->chunkstat;
+    p.lunit32 = h->lunit32;
+    p.extras = h->extras;
+    p.extn = h->extn;
     p.chunkbase = h->chunkbase;
+    p.vfirst = h->vfirst;
     p.bucket = h->bucket;
     p.cnt = h->cnt;
     p.ovf = h->ovf;
@@ -626,13 +693,13 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.nframes = B;
     p.f_in = f_in;
     p.f_out = f_out;
-    p.T = h->cfg.max_num_points;
+    p.T = T;
     p.cap = cap;
     p.overflow_continue = h->cfg.overflow_mode == BVX_OVERFLOW_CONTINUE;
     p.coor_cols = o.coor_cols;
     p.frame_base = o.frame_base;
     p.ovf_cap = h->cfg.max_points;
-    p.vec4 = (f_in == 4 && aligned) ? 1 : 0;
+    p.vec4 = vec4 ? 1 : 0;
     p.clear_rows = 0;
     p.voxels = o.voxels;
     p.idx_out = o.idx;
@@ -642,20 +709,19 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.num_points = o.num_points;
     p.mean_out = o.mean;
     p.mean_c = o.mean_c;
+    p.inline_frames = B <= kInlineFrames ? 1 : 0;
+    if (p.inline_frames) memcpy(p.inl, h->h_frames.data(), sizeof(FrameDesc) * (size_t)B);
 
-    const int T = p.T;
-    const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
     const bool hashed = h->cfg.grid_kind == BVX_GRID_HASHED;
     const int rchunks = hashed ? 0 : chunks;            // per-entry reset blocks (dense grid only)
     if (hashed && chunks > 0) {
-        // one clear row per 64 KB of the largest frame's table (measured: 16 KB .. 256 KB slices are
+        // one clear slice per 64 KB of the largest frame's table (measured: 16 KB .. 256 KB slices are
         // within 2 % of each other at 64 frames; small slices keep the single-frame latency down)
         const unsigned long long tbytes = (1ull << h->max_tbl_lg) * 8;
         p.clear_rows = (int)std::max<unsigned long long>(1, std::min<unsigned long long>(256, tbytes / (64 * 1024)));
     }
-    if (chunks > 65535 - 256 || B > 65535)
-        return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 65535 frames per call and 67M points per frame");
-    (void)max_words;
+    cudaError_t le = cudaSuccess;
+    auto note = [&](cudaError_t e) { if (le == cudaSuccess) le = e; };
     if (chunks > 0) {
         ProfScope ps(h, 0, st);
         bool crop = false;
@@ -664,56 +730,49 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         // more rows than the largest frame has chunks
         const int rows = std::min(chunks, insert_rows_bound(B));
         const dim3 grid(B, p.clear_rows + rows);
-        if (crop) launch_k(h, k_insert<true>, grid, kBlock, 0, st, p);
-        else launch_k(h, k_insert<false>, grid, kBlock, 0, st, p);
+        if (crop) note(launch_k(h, k_insert<true>, grid, kBlock, 0, st, p));
+        else note(launch_k(h, k_insert<false>, grid, kBlock, 0, st, p));
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
-        // one warp per chunk, and enough blocks that none clears more than 8192 bucket entries
-        const long long clr = (long long)std::min(cap, max_n) * (T <= kChainMaxT ? T : 1);
-        const int vgx = (int)std::min<long long>(65535, std::max<long long>((std::max(chunks, 1) + kWarps - 1) / kWarps,
-                                                                            (clr + 8191) / 8192));
-        launch_k(h, k_verify, dim3(vgx, B), kBlock, 0, st, p);
-    }
-    if (chunks > 0) {
-        { ProfScope ps(h, 3, st); const int sgx = p.overflow_continue ? chunks : 48;   // measured: break is flat from 32 to 64, continue wants all chunks
-          launch_k(h, k_slot, dim3(std::min(chunks, std::max(sgx, (148 * 8 + B - 1) / B)), B), kBlock, 0, st, p); }
-        if (T > kChainMaxT) {
-            const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
-            ProfScope ps(h, 4, st);
-            k_overflow<<<ob, kBlock, 0, st>>>(p);
+        // one warp per chunk for the numbering, all resident at once (148 SMs x 8 blocks), + 1 publisher per frame
+        const int gx = std::max(1, std::min((chunks + kWarps - 1) / kWarps, std::max(2, 148 * 8 / B - 1)));
+        const int n2e = 0;
+        if (chunks > h->scan_smem_chunks) {
+            k_scan_big<<<B, kBlock, 0, st>>>(p);
             g_launches += 1;
+            note(cudaGetLastError());
+            note(launch_k(h, k_mid<true>, dim3(gx + 1, B), kBlock, 0, st, p, 0, n2e));
+        } else {
+            const int sc = (std::max(chunks, 1) + 3) & ~3;
+            note(launch_k(h, k_mid<false>, dim3(gx + 1, B), kBlock, ((size_t)sc * 10 + 8 + 15) & ~(size_t)15, st, p, sc, n2e));
         }
     }
-    const bool small = T <= kChainMaxT && f_out == 4 && p.vec4 && h->all_plain;
-    if (o.crow && !small)
-        return fail(h, BVX_ERR_BAD_ARGUMENT, "compact rows need the specialised gather (T <= 8, 4 aligned features)");
+    if (chunks > 0 && T > kChainMaxT) {
+        const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
+        ProfScope ps(h, 4, st);
+        k_overflow<<<ob, kBlock, 0, st>>>(p);
+        g_launches += 1;
+        note(cudaGetLastError());
+    }
     if (small) {
         const int tiles = (cap + kBlock - 1) / kBlock;
         const size_t smem = (size_t)kWarps * 32 * T * 16;
         const dim3 grid(tiles + rchunks, B);
         ProfScope ps(h, 5, st);
         switch (T) {
-#define BVX_GS(TT) case TT: launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p, tiles); break;
+#define BVX_GS(TT) case TT: note(launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p, tiles)); break;
             BVX_GS(1) BVX_GS(2) BVX_GS(3) BVX_GS(4) BVX_GS(5) BVX_GS(6) BVX_GS(7) BVX_GS(8)
 #undef BVX_GS
         }
     } else {
-        // voxels per tile: ~256 bucket entries, ~1024 for long buckets (few of their entries are live)
-        int vt = std::max(1, (T > 32 ? 1024 : kBlock) / T);
-        auto tile_smem = [&](int v) {
-            return (size_t)(((v * T + 3) & ~3) + ((v + 3) & ~3)) * 4 + (size_t)v * T * f_out * 4;
-        };
-        while (vt > 1 && tile_smem(vt) > 48 * 1024) vt >>= 1;
-        const int tiles = (cap + vt - 1) / vt;
-        const size_t smem = tile_smem(vt);
-        if (smem > 200 * 1024)
-            return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", smem);
-        if (smem > 48 * 1024)
-            CK(h, cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int tiles = (cap + gather_vt - 1) / gather_vt;
+        if (gather_smem > 48 * 1024)
+            note(cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gather_smem));
         ProfScope ps(h, 5, st);
-        launch_k(h, k_gather, dim3(tiles + rchunks, B), kBlock, smem, st, p, tiles, vt);
+        note(launch_k(h, k_gather, dim3(tiles + rchunks, B), kBlock, gather_smem, st, p, tiles, gather_vt));
     }
+    if (le != cudaSuccess) return fail(h, BVX_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(le));
     CK(h, cudaGetLastError());
     return BVX_OK;
 }

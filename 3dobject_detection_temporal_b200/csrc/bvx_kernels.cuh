@@ -2,22 +2,24 @@
 //
 // Pipeline (one pass of VoxelGenerator.generate over B frames; DESIGN.md has the
 // data layout and the per-kernel roofline).  Work is cut into chunks of 1024
-// consecutive points (256 threads x 4 points, all four loads in flight at once):
+// consecutive points (256 threads x 4 points; a warp owns 128 consecutive points =
+// one "unit" of four 32-point bit words):
 //   k_insert  per chunk : cell key -> table slot; first occurrence by 64-bit
 //                         atomicCAS/atomicMin on {cell:32 | point index:32};
-//                         candidate bit per point ("held the minimum when I left")
-//   k_verify  per chunk : candidate -> true first-occurrence bits, per-word and
-//                         per-chunk counts; the LAST chunk of a frame scans the
-//                         chunk counts (first-come voxel ranks, M = min(total,
-//                         cap), break cut-off i*), the last frame prefix-sums M
-//   k_slot    per chunk : voxel id = rank of the voxel's first point; slot inside
-//                         the voxel in input order (sorted atomicMin chain for
-//                         T <= 8, count + bucket for larger T)
+//                         candidate bit per point ("held the minimum when I left"),
+//                         `lost` bit for a candidate displaced later; every in-range
+//                         point that is NOT the first of its cell goes, with its
+//                         table slot, onto the chunk's compact "extras" list
+//   k_mid     per chunk : scan of the per-chunk first-occurrence counts (every block,
+//                         in shared memory) -> voxel number of every first point
+//                         (written as vfirst[voxel]), M = min(total, cap), the break
+//                         cut-off i*; then only the EXTRAS (the 2nd, 3rd ... point of
+//                         a cell) look their voxel up and take their slot by a sorted
+//                         atomicMin chain (T <= 8) or count + bucket (larger T)
 //   k_overflow          : (T > 8) T-smallest selection for crowded voxels
 //   k_gather  per voxel : rows -> voxels (zero padded), coordinates from the first
-//                         point, num_points, optional fused mean VFE; extra blocks
-//                         of the same launch reset the table entries the frame
-//                         touched, so the next call needs no memset
+//                         point, num_points, optional fused mean VFE; puts every
+//                         per-call structure back into its between-calls state
 // Everything is fp32 / int32; nothing here is a contraction, hence no tensor
 // cores: the bounds are HBM bandwidth and L2 random-access / atomic throughput.
 #pragma once
@@ -27,31 +29,42 @@
 namespace bvx {
 
 constexpr unsigned long long kEmpty64 = 0xFFFFFFFFFFFFFFFFull;
-constexpr int kEmptyIdx = 0x7FFFFFFF;
+constexpr int kEmptyIdx = 0x7F7F7F7F;  // empty bucket entry (a cudaMemset pattern); > every point index
+constexpr int kMaxFramePoints = 0x7F000000;
 constexpr int kChainMaxT = 8;        // T <= 8: sorted atomicMin chain; else count+bucket
 constexpr int kBlock = 256;
 constexpr int kPts = 4;              // points per thread
 constexpr int kChunk = kBlock * kPts;  // 1024 points per chunk
 constexpr int kChunkWords = kChunk / 32;
 constexpr int kWarps = kBlock / 32;
+constexpr int kUnit = 32 * kPts;     // 128 points: what one warp owns of a chunk
+constexpr int kScanSmemChunks = 4096;  // frames up to this many chunks are scanned in shared memory by k_mid
+constexpr int kInlineFrames = 64;      // calls of up to this many frames carry their frame descriptors as kernel arguments
+#ifndef BVX_ABL
+#define BVX_ABL 0   // timing ablations of experiment builds (tools/variants.sh); 0 in the product
+#endif
+#ifndef BVX_INSERT_BLOCKS
+#define BVX_INSERT_BLOCKS 6   // 42 registers, no spills: 59.6 us against 76.4 us with 8 blocks of 32 registers (cfg4 break)
+#endif
 
 struct GridParams {
     float lo[3];
     float vs[3];
+    float rvs[3];  // 1 / vs rounded to nearest (NaN: always take the exact divide)
     float gsf[3];  // grid size as float, x y z
     int gs[3];     // x y z
 };
 
 struct FrameDesc {
-    const float* pts0;           // points of the frame when it is ONE plain segment, else null
+    long long pts_off;           // plain frame: float offset of its first row from Pipe::base
     unsigned long long tbl_off;  // entry offset of this frame's table region
     unsigned int tbl_mask;       // slots - 1 (hashed)
     int tbl_shift;               // 32 - log2(slots) (hashed); -1 => dense (slot = cell)
     int n;                       // points in the frame (all segments)
-    int pt_off;                  // base into slot[]
-    int word_off;                // base into cand/first/wordlocal
+    int plain;                   // ONE segment, no transform / dt / permutation / crop: rows are read from base + pts_off
+    int word_off;                // base into cand / lost (multiple of 4)
     int nwords;
-    int chunk_off;               // base into chunkbase[]
+    int chunk_off;               // base into chunkstat / extn / chunkbase; x8 into unit8; x1024 into extras
     int nchunks;
     int seg_begin;
     int seg_count;
@@ -75,14 +88,14 @@ struct FrameState {
     int total;        // distinct in-range cells among the inserted points
     int m;            // voxels kept = min(total, cap)
     int istar;        // break cut-off: points with index >= istar are dropped
-    int done_verify;  // chunks of k_verify finished (last-block detection); reset by the scanner
+    int clear_claim;  // k_insert: table slices handed out so far (hashed grid)
     unsigned long long ticket;  // k_insert: bits 0-30 = next chunk of the frame to hand out (in index order),
                                 // bit 31 = table known to be empty, high 32 bits = cells claimed so far --
                                 // one atomic returns all three
     int n_eff;        // k_insert: start of the first chunk skipped by the break early exit
-    int n_done;       // points that went through k_insert (prefix), published by the scan
-    int cleared;      // k_insert: table slices cleared so far (hashed grid); reset by k_slot
-    int rows;         // k_gather_small, compact-row mode: kept points of the frame (reset by the frame scan)
+    int n_done;       // points that went through k_insert (prefix), published by k_mid
+    int cleared;      // k_insert: table slices cleared so far (hashed grid)
+    int rows;         // k_gather_small, compact-row mode: kept points of the frame (reset by k_mid)
 };
 
 struct Pipe {
@@ -90,15 +103,20 @@ struct Pipe {
     const FrameDesc* frames;
     const SegDesc* segs;
     FrameState* state;
+    const float* base;   // plain frames: rows start at base + FrameDesc::pts_off
     unsigned long long* table;
-    int* slot;           // per point: index of the first point of its cell as seen when it was inserted (-1: out of range)
     unsigned int* cand;
     unsigned int* lost;  // per point bit: was the cell's first point for a while, then displaced by an earlier one
-    unsigned int* first;
-    int* wordlocal;      // exclusive prefix of first-occurrence counts inside the word's chunk
-    int* chunkbase;      // per chunk: count, then exclusive prefix over the frame's chunks
-    int* bucket;
-    int* cnt;
+    unsigned char* unit8;     // per 128-point unit: number of candidate bits (0 .. 128)
+    unsigned int* chunkstat;  // per chunk: first occurrences (low 16 bits) | displaced candidates (high 16)
+    unsigned int* lunit32;    // per chunk two words = eight bytes: displaced candidates per unit (between calls: 0)
+    int2* extras;        // per chunk, 1024 entries: {point index, table slot of its cell} of every in-range point
+                         // that is not the first of its cell (as seen when it was inserted, or displaced later)
+    int* extn;           // per chunk: entries on its extras list
+    int* chunkbase;      // frames of more than kScanSmemChunks chunks only: exclusive prefix of the chunk counts
+    int* vfirst;         // [B, cap] point index of the first point of every voxel
+    int* bucket;         // [B, cap, T-1] the other kept points of a voxel (between calls: all kEmptyIdx for T <= 8)
+    int* cnt;            // [B, cap] T > 8: points beyond the first seen by the voxel (between calls: all 0)
     int2* ovf;
     int* counters;       // [0] frames-done ticket, [1] overflow count, [2] compact rows handed out
     int* frame_voxel_offsets;
@@ -113,7 +131,7 @@ struct Pipe {
     int frame_base;      // batch index of frame 0 of this call (sub-batches of a pipelined host call)
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
-    int clear_rows;      // hashed tables: the first clear_rows block rows of k_insert clear the tables (0: dense grid)
+    int clear_rows;      // hashed tables: slices each table is cleared in = leading block rows of k_insert (0: dense grid)
     // outputs
     float4* crow;        // optional, specialised gather only: the kept rows of the call, compact (no padding): a tile
                          // of 256 voxels owns the range starting at tile_base[frame * tiles + tile] (ranges are
@@ -127,7 +145,15 @@ struct Pipe {
     int* num_points;
     float* mean_out;
     int mean_c;
+    int inline_frames;   // frame descriptors are in inl[] (constant bank: no load chain at block start, no upload)
+    FrameDesc inl[kInlineFrames];
 };
+
+__device__ __forceinline__ FrameDesc frame_desc(const Pipe& p, int f)
+{
+    if (p.inline_frames) return p.inl[f];
+    return p.frames[f];
+}
 
 // Programmatic dependent launch: every pipeline kernel lets its successor start being scheduled as
 // soon as all of its own blocks are resident (the successor's blocks then fill the SM slots the last
@@ -158,13 +184,29 @@ __device__ __forceinline__ void xform(const SegDesc& sg, float& x, float& y, flo
     }
 }
 
-// floor((p - lo) / size) in fp32 with IEEE subtract/divide; -1 if outside / NaN.
-// Linear cell index in the reference's zyx grid order.
+// floor(RN((v - lo) / size)), the reference's fp32 expression, without the divide where its result
+// is certain.  a = RN(v - lo); t = RN(a * RN(1/size)) differs from the correctly rounded quotient q
+// by less than 2^-22 |t| (three roundings of 2^-24 each), so whenever t lies further than
+// m = 2^-21 |t| from both neighbouring integers, floor(q) == floor(t).  Otherwise (about one point in a
+// thousand; also NaN, Inf, zero, |t| >= 2^21, a size whose reciprocal is not a normal number) the IEEE
+// divide decides.
+__device__ __forceinline__ float cell_axis(float v, float lo, float vs, float rvs)
+{
+    const float a = __fsub_rn(v, lo);
+    const float t = __fmul_rn(a, rvs);
+    float k = floorf(t);
+    const float fr = __fsub_rn(t, k);                                  // exact
+    const float m = __fmul_rn(fabsf(t), 4.76837158203125e-07f);        // 2^-21 |t|
+    if (!(fminf(fr, __fsub_rn(1.0f, fr)) > m)) k = floorf(__fdiv_rn(a, vs));
+    return k;
+}
+
+// -1 if outside / NaN, else the linear cell index in the reference's zyx grid order.
 __device__ __forceinline__ int cell_of(const GridParams& g, float x, float y, float z)
 {
-    const float cx = floorf(__fdiv_rn(__fsub_rn(x, g.lo[0]), g.vs[0]));
-    const float cy = floorf(__fdiv_rn(__fsub_rn(y, g.lo[1]), g.vs[1]));
-    const float cz = floorf(__fdiv_rn(__fsub_rn(z, g.lo[2]), g.vs[2]));
+    const float cx = cell_axis(x, g.lo[0], g.vs[0], g.rvs[0]);
+    const float cy = cell_axis(y, g.lo[1], g.vs[1], g.rvs[1]);
+    const float cz = cell_axis(z, g.lo[2], g.vs[2], g.rvs[2]);
     const bool ok = (cx >= 0.0f) && (cx < g.gsf[0]) && (cy >= 0.0f) && (cy < g.gsf[1]) &&
                     (cz >= 0.0f) && (cz < g.gsf[2]);
     if (!ok) return -1;
@@ -192,18 +234,24 @@ __device__ __forceinline__ bool cropped_out(const SegDesc& sg, float x, float y,
     return out;
 }
 
+__device__ __forceinline__ const float* plain_rows(const Pipe& p, const FrameDesc& fr)
+{
+    return p.base + fr.pts_off;
+}
+
 // xyz of frame-local point i (sweep transform applied).  CROP: also apply the frame's crop planes
 // (only k_insert needs that: every later kernel only looks at points that got a cell).
 template <bool CROP = false>
 __device__ __forceinline__ void load_xyz(const Pipe& p, const FrameDesc& fr, int i, float& x, float& y,
                                          float& z)
 {
-    if (fr.pts0) {
+    if (fr.plain) {
+        const float* q0 = plain_rows(p, fr);
         if (p.vec4) {
-            const float4 v = __ldcs(reinterpret_cast<const float4*>(fr.pts0) + i);  // streamed once
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(q0) + i);  // streamed once
             x = v.x; y = v.y; z = v.z;
         } else {
-            const float* q = fr.pts0 + (size_t)i * p.f_in;
+            const float* q = q0 + (size_t)i * p.f_in;
             x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
         }
         return;
@@ -226,8 +274,8 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 {
     const float* q;
     const SegDesc* sg = nullptr;
-    if (fr.pts0) {
-        q = fr.pts0 + (size_t)i * p.f_in;
+    if (fr.plain) {
+        q = plain_rows(p, fr) + (size_t)i * p.f_in;
     } else {
         sg = &find_seg(p, fr, i);
         const int j = sg->perm ? __ldg(sg->perm + (i - sg->start)) : i - sg->start;
@@ -251,10 +299,10 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 
 // ---------------------------------------------------------------- k_insert
 // grid (B, clear rows + chunk rows): x = frame, so blocks are dispatched row by row across all
-// frames: first the rows that clear the tables, then the (persistent) chunk rows.  A block takes the frame's next chunk in index order
-// from a ticket counter.  Thread t of chunk c owns points c*1024 + k*256 + t,
-// k = 0..3: every warp-wide access is coalesced and a warp covers exactly one
-// 32-point mask word per k.
+// frames: first the rows that clear the tables, then the (persistent) chunk rows.  A block takes
+// the frame's next chunk in index order from a ticket counter.  Warp w of chunk c owns points
+// c*1024 + w*128 + k*32 + lane, k = 0..3: every warp-wide access is coalesced, a warp covers four
+// consecutive 32-point mask words.
 //
 // Break early exit (the reference's serial loop stops at the point that would open
 // voxel #cap): the ticket counter carries, in its high half, the number of distinct
@@ -263,7 +311,11 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // every cell it counts was claimed by a chunk with a smaller ticket, so the cut-off
 // index i* lies before this chunk and the chunk is skipped (nothing it holds can be
 // kept).  The count only grows, so skipping is monotone in the ticket and the
-// inserted points always form a prefix [0, n_eff).
+// inserted points always form a prefix [0, n_eff).  The ticket of the NEXT chunk is taken
+// by the first warp as soon as its own insert rounds are over, so its round trip overlaps
+// the epilogue and the wait for the other warps (one block barrier per chunk).  (Taking it
+// at the START of the current chunk hid it completely but made the count one chunk old:
+// 83 instead of 63 chunks per frame were processed before the exit, cfg4.)
 //
 // Table protocol, CAS first, in ROUNDS (one atomic per point in flight, 4 per
 // thread):
@@ -272,75 +324,95 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 //                                   other cell  -> probe the next slot
 // A point whose atomicMin displaces the entry of a later point marks that point in the
 // `lost` bitmap, so after the kernel   first = cand & ~lost   holds exactly the points that
-// are still table entries -- no pass over the table is needed to find them.  Every point
-// also records the first point of its cell as it saw it (slot[]); k_slot trusts that
-// record iff the recorded point is still a first point.
-template <bool CROP>
-__global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
+// are still table entries -- no pass over the table is needed to find them.  Every in-range
+// point that is not a candidate when it leaves, and every displaced point (recorded by its
+// displacer), goes on the chunk's extras list with the table slot of its cell: those are all
+// the points that are not the first of their voxel, and only they need a pass of their own.
+// (Recording the first point as seen instead of the slot saves k_mid the table access only for
+// warps in which no lane's record went stale -- one warp in ten: measured slower.)
+__device__ __forceinline__ void clear_slice(const Pipe& p, const FrameDesc& fr, int s)
 {
-    __shared__ int s_chunk, s_ready;
+    const unsigned int n2 = (fr.tbl_mask + 1u) >> 1;        // uint4 = two slots
+    const unsigned int per = (n2 + p.clear_rows - 1) / p.clear_rows;
+    const unsigned int lo = min(n2, (unsigned)s * per), hi = min(n2, lo + per);
+    uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
+    const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+    for (unsigned int j = lo + threadIdx.x; j < hi; j += kBlock) t4[j] = e;
+}
+
+template <bool CROP>
+__global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert(const __grid_constant__ Pipe p)
+{
+    __shared__ int s_tk[2], s_rdy[2], s_extn[2], s_slice;
     pdl_prologue();
     const int f = blockIdx.x;
-    const FrameDesc fr = p.frames[f];
+    const FrameDesc fr = frame_desc(p, f);
     FrameState* st = p.state + f;
     if ((int)blockIdx.y < p.clear_rows) {
         // Clear rows: the frame's table is emptied here, right before it is used, with normal
         // stores -- whole sectors, so the lines are allocated in the L2 without a DRAM fill and
-        // the atomics below find them there.  These blocks never wait, so the insert blocks of
-        // the frame (later in dispatch order) can safely wait for them.
+        // the atomics below find them there.  Slices are CLAIMED (not owned by block index): an
+        // insert block that finds the table not ready claims slices too, so it only ever waits
+        // for blocks that are already running -- no assumption about the dispatch order.
         if (fr.n > 0) {
-            const unsigned int n2 = (fr.tbl_mask + 1u) >> 1;        // uint4 = two slots
-            const unsigned int per = (n2 + p.clear_rows - 1) / p.clear_rows;
-            const unsigned int lo = blockIdx.y * per, hi = min(n2, lo + per);
-            uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
-            const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-            for (unsigned int j = lo + threadIdx.x; j < hi; j += kBlock) t4[j] = e;
-            __threadfence();
+            if (threadIdx.x == 0) s_slice = atomicAdd(&st->clear_claim, 1);
             __syncthreads();
-            if (threadIdx.x == 0) atomicAdd(&st->cleared, 1);
+            if (s_slice < p.clear_rows) {
+                clear_slice(p, fr, s_slice);
+                __threadfence();
+                __syncthreads();
+                if (threadIdx.x == 0) atomicAdd(&st->cleared, 1);
+            }
         }
         return;
     }
     if ((int)(blockIdx.y - p.clear_rows) * kChunk >= fr.n) return;
     const bool brk = !p.overflow_continue;
     unsigned long long* tbl = p.table + fr.tbl_off;
-    // Chunk rows are persistent: a block keeps taking tickets of its frame until the frame is
-    // exhausted or cut, so the launch carries (rows x frames) blocks, not one block per chunk.
-  for (;;) {
-    if (threadIdx.x == 0) {
-        const unsigned long long t = atomicAdd(&st->ticket, 1ull);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int toff = wid * kUnit + lane;                 // this thread's first point inside a chunk
+    // ticket -> (chunk, table-ready flag); a chunk past the break cut-off is skipped
+    auto take = [&](unsigned long long t, int q) {
         int c = (int)((unsigned int)t & 0x7FFFFFFFu);
-        s_ready = (int)(((unsigned int)t >> 31) | (p.clear_rows == 0));   // bit 31: the table is known to be empty
-        if (brk && (int)(t >> 32) > p.cap && c * kChunk < fr.n) {
+        s_rdy[q] = (int)(((unsigned int)t >> 31) | (p.clear_rows == 0));   // bit 31: the table is known to be empty
+        if (brk && (int)(t >> 32) > p.cap && (long long)c * kChunk < fr.n) {
             atomicMin(&st->n_eff, c * kChunk);
             c = 0x7FFFFFF;                             // skipped
         }
-        s_chunk = c;
+        s_tk[q] = c;
+    };
+    if (threadIdx.x == 0) {
+        s_extn[0] = 0; s_extn[1] = 0;
+        take(atomicAdd(&st->ticket, 1ull), 0);
     }
     __syncthreads();
-    const long long basel = (long long)s_chunk * kChunk;
-    const int ready = s_ready;
+    // Chunk rows are persistent: a block keeps taking tickets of its frame until the frame is
+    // exhausted or cut, so the launch carries (rows x frames) blocks, not one block per chunk.
+  for (int it = 0;; ++it) {
+    const int q = it & 1;
+    const long long basel = (long long)s_tk[q] * kChunk;
+    const int ready = s_rdy[q];
     if (basel >= fr.n) return;
     const int base = (int)basel;
     int cell[kPts];
     unsigned int h[kPts];
-    if (!CROP && fr.pts0 && p.vec4) {
+    if (!CROP && fr.plain && p.vec4) {
         // plain frame of float4 points: all four loads are issued before the first one is used
         // (one DRAM round trip per chunk, not four)
-        const float4* q = reinterpret_cast<const float4*>(fr.pts0) + base + threadIdx.x;
+        const float4* qp = reinterpret_cast<const float4*>(plain_rows(p, fr)) + base + toff;
         float4 v[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (base + k * kBlock + (int)threadIdx.x < fr.n) v[k] = __ldcs(q + k * kBlock);   // streamed once
+            if (base + toff + k * 32 < fr.n) v[k] = __ldcs(qp + k * 32);   // streamed once
         }
 #pragma unroll
         for (int k = 0; k < kPts; ++k)
-            cell[k] = (base + k * kBlock + (int)threadIdx.x < fr.n) ? cell_of(p.g, v[k].x, v[k].y, v[k].z) : -1;
+            cell[k] = (base + toff + k * 32 < fr.n) ? cell_of(p.g, v[k].x, v[k].y, v[k].z) : -1;
     } else {
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
-            const int i = base + k * kBlock + threadIdx.x;
+            const int i = base + toff + k * 32;
             cell[k] = -1;
             if (i < fr.n) {
                 float x, y, z;
@@ -351,12 +423,27 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
     }
     if (!ready) {
         // The table must be empty before the first atomic (the point loads above did not need it).
-        // The first block of a frame to see all clear rows done says so in bit 31 of the ticket
-        // word; blocks that get the bit with their ticket skip this wait and its barrier.  (The clear
-        // stores were fenced to the L2 before `cleared` was bumped, and the table is only ever
-        // touched by atomics, which act at the L2.)
+        // Help with whatever slices are still unclaimed, then wait for the claimed ones (their
+        // blocks are running).  The first block of a frame to see all slices done says so in bit 31
+        // of the ticket word; blocks that get the bit with their ticket skip all of this.  (The
+        // clear stores were fenced to the L2 before `cleared` was bumped, and the table is only
+        // ever touched by atomics, which act at the L2.)
+        if (threadIdx.x == 0) s_slice = *(volatile int*)&st->cleared >= p.clear_rows ? -1 : 0;
+        __syncthreads();
+        if (s_slice != -1) {
+            for (;;) {
+                __syncthreads();
+                if (threadIdx.x == 0) s_slice = atomicAdd(&st->clear_claim, 1);
+                __syncthreads();
+                if (s_slice >= p.clear_rows) break;
+                clear_slice(p, fr, s_slice);
+                __threadfence();
+                __syncthreads();
+                if (threadIdx.x == 0) atomicAdd(&st->cleared, 1);
+            }
+            if (threadIdx.x == 0) while (*(volatile int*)&st->cleared < p.clear_rows) { }
+        }
         if (threadIdx.x == 0) {
-            while (*(volatile int*)&st->cleared < p.clear_rows) { }
             __threadfence();
             atomicOr(&st->ticket, 0x80000000ull);
         }
@@ -372,13 +459,13 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
             active |= 1u << k;
         }
     }
-    // (a straight-line, select-based first round in front of this loop measured slower: 62.4 vs 59.3 us)
+    int2* ext = p.extras + (size_t)(fr.chunk_off + (base >> 10)) * kChunk;
     while (__any_sync(0xffffffffu, active)) {          // warp-uniform rounds
         unsigned long long r[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             const unsigned long long mine = ((unsigned long long)(unsigned)cell[k] << 32) |
-                                            (unsigned)(base + k * kBlock + threadIdx.x);
+                                            (unsigned)(base + toff + k * 32);
             r[k] = 0;
             if (active & (1u << k))
                 r[k] = (needmin & (1u << k)) ? atomicMin(tbl + h[k], mine)
@@ -388,23 +475,24 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
         for (int k = 0; k < kPts; ++k) {
             const unsigned int bit = 1u << k;
             if (!(active & bit)) continue;
-            const unsigned int i = (unsigned)(base + k * kBlock + threadIdx.x);
-            // a point that is done keeps, in h[k], the first point of its cell as it saw it
+            const unsigned int i = (unsigned)(base + toff + k * 32);
+            // a point that is done keeps, in h[k], the table slot of its cell
             if (needmin & bit) {
                 const unsigned int o = (unsigned)r[k];
                 if (o > i) {
+                    // I am the cell's first point now; o no longer is: it becomes an extra of the
+                    // cell, its chunk counts one first point less and one displaced candidate more
                     wonmask |= bit;
-                    atomicOr(p.lost + fr.word_off + (o >> 5), 1u << (o & 31));   // o is no longer first
-                    h[k] = i;
-                } else {
-                    h[k] = o;
+                    atomicOr(p.lost + fr.word_off + (o >> 5), 1u << (o & 31));
+                    atomicAdd(p.chunkstat + fr.chunk_off + (o >> 10), 0xFFFFu);
+                    atomicAdd(p.lunit32 + (size_t)(fr.chunk_off + (o >> 10)) * 2 + ((o >> 9) & 1u), 1u << (((o >> 7) & 3u) * 8));
+                    ext[atomicAdd(&s_extn[q], 1)] = make_int2((int)o, (int)h[k]);
                 }
                 active &= ~bit;
             } else if (r[k] == kEmpty64) {
                 wonmask |= bit; ++nnew; active &= ~bit;
-                h[k] = i;
             } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
-                if ((unsigned)r[k] > i) needmin |= bit; else { active &= ~bit; h[k] = (unsigned)r[k]; }
+                if ((unsigned)r[k] > i) needmin |= bit; else active &= ~bit;
             } else {
                 h[k] = (h[k] + 1) & fr.tbl_mask;
             }
@@ -414,21 +502,60 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : 8) k_insert(const Pipe p)
         // publish the cells this warp claimed (per warp, as soon as it is done: measured better
         // than one add per block); later tickets see them in their ticket word
         nnew = __reduce_add_sync(0xffffffffu, nnew);
-        if (nnew && (threadIdx.x & 31) == 0) atomicAdd(&st->ticket, (unsigned long long)nnew << 32);
+        if (nnew && lane == 0) atomicAdd(&st->ticket, (unsigned long long)nnew << 32);
     }
+    // The next chunk's ticket is taken here, by the first warp when ITS rounds are over: the claimed-cell
+    // count it carries is fresh, and its round trip overlaps the epilogue and the wait for the other warps.
+    unsigned long long tnext = 0;
+    if (threadIdx.x == 0) tnext = atomicAdd(&st->ticket, 1ull);
+    {
+        // candidate words of the warp's unit (one 16-byte store), their count, and the warp's own
+        // extras: in range, not a candidate
+        unsigned int cw[kPts], ew[kPts];
+        int ncand = 0, next = 0;
 #pragma unroll
-    for (int k = 0; k < kPts; ++k) {
-        const int i = base + k * kBlock + threadIdx.x;
-        if (i < fr.n) p.slot[fr.pt_off + i] = cell[k] >= 0 ? (int)h[k] : -1;
-        const unsigned int b = __ballot_sync(0xffffffffu, (wonmask >> k) & 1u);
-        const int w = i >> 5;
-        if ((threadIdx.x & 31) == 0 && w < fr.nwords) p.cand[fr.word_off + w] = b;
+        for (int k = 0; k < kPts; ++k) {
+            cw[k] = __ballot_sync(0xffffffffu, (wonmask >> k) & 1u);
+            ew[k] = __ballot_sync(0xffffffffu, cell[k] >= 0 && !((wonmask >> k) & 1u));
+            ncand += __popc(cw[k]);
+            next += __popc(ew[k]);
+        }
+        const int cidx = fr.chunk_off + (base >> 10);
+        const int w0 = (base >> 5) + wid * kPts;                    // first word of the unit (frame-local)
+        if (lane == 0) {
+            if (w0 + kPts <= fr.nwords) {
+                *reinterpret_cast<uint4*>(p.cand + fr.word_off + w0) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < kPts; ++k)
+                    if (w0 + k < fr.nwords) p.cand[fr.word_off + w0 + k] = cw[k];
+            }
+            p.unit8[(size_t)cidx * kWarps + wid] = (unsigned char)ncand;
+            if (ncand) atomicAdd(p.chunkstat + cidx, (unsigned)ncand);
+        }
+        if (next) {
+            int eb = 0;
+            if (lane == 0) eb = atomicAdd(&s_extn[q], next);
+            eb = __shfl_sync(0xffffffffu, eb, 0);
+            const unsigned int below = (1u << lane) - 1u;
+#pragma unroll
+            for (int k = 0; k < kPts; ++k) {
+                if ((ew[k] >> lane) & 1u)
+                    ext[eb + __popc(ew[k] & below)] = make_int2(base + toff + k * 32, (int)h[k]);
+                eb += __popc(ew[k]);
+            }
+        }
     }
-    __syncthreads();        // s_chunk / s_ready are rewritten by the next round
+    if (threadIdx.x == 0) take(tnext, q ^ 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        p.extn[fr.chunk_off + (base >> 10)] = s_extn[q];
+        s_extn[q] = 0;                  // next used two iterations from now, behind the next barrier
+    }
   }
 }
 
-// ---------------------------------------------------------------- k_verify
+// ---------------------------------------------------------------- scans
 __device__ __forceinline__ int warp_exclusive_scan(int v, int lane, int* total)
 {
     int inc = v;
@@ -460,72 +587,18 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* smem
     return base + ex;
 }
 
-// Frame-level part, run by the last chunk of the frame to finish k_verify: scan the
-// chunk counts in place (chunkbase becomes the exclusive prefix), publish total / M /
-// i*, and -- for the last frame of the call -- the exclusive prefix of M over frames.
-__device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, int* sm)
+// Exclusive prefix over the frames of M (frame_voxel_offsets) by the block that finished the
+// call's last frame; puts the call-level counters back.
+__device__ void frames_done(const Pipe& p, int* sm)
 {
-    const int nchunks = (eff + kChunk - 1) / kChunk, nwords = (eff + 31) / 32;
-    int* cb = p.chunkbase + fr.chunk_off;
-    const int cap = p.cap;
-    int carry = 0;
-    int cut_chunk = -1, cut_base = 0;
-    for (int b0 = 0; b0 < nchunks; b0 += kBlock) {
-        const int c = b0 + threadIdx.x;
-        const int v = c < nchunks ? __ldcg(cb + c) : 0;
-        int tot;
-        const int ex = carry + block_exclusive_scan(v, &tot, sm);
-        if (c < nchunks) {
-            cb[c] = ex;
-            if (ex <= cap && cap < ex + v) { cut_chunk = c; cut_base = ex; }  // at most one thread
-        }
-        carry += tot;
-    }
-    const int total = carry;
-    const bool cut = (!p.overflow_continue) && total > cap;
-    if (threadIdx.x == 0) {
-        p.state[f].total = total;
-        p.state[f].m = min(total, cap);
-        p.state[f].done_verify = 0;            // ready for the next call
-        p.state[f].rows = 0;
-        p.state[f].n_done = eff;
-        if (!cut) p.state[f].istar = eff;
-    }
-    {
-        // The point that would open voxel #cap: the (cap - prefix)-th first occurrence of the cut
-        // chunk.  At most one thread found that chunk; broadcast it, then warp 0 searches the
-        // chunk's 32 words with one load per lane.
-        __shared__ int s_cut[2];
-        if (threadIdx.x == 0) s_cut[0] = -1;
-        __syncthreads();
-        if (cut_chunk >= 0) { s_cut[0] = cut_chunk; s_cut[1] = cut_base; }
-        __syncthreads();
-        if (cut && s_cut[0] >= 0 && threadIdx.x < 32) {
-            const int cc = s_cut[0];
-            int need = cap - s_cut[1];
-            const int w0 = fr.word_off + cc * kChunkWords;
-            const int nw = min(kChunkWords, nwords - cc * kChunkWords);
-            const int lane = threadIdx.x;
-            // word w holds the target iff wordlocal[w] <= need < wordlocal[w + 1]; 32 words, one per lane
-            const int lo = lane < nw ? __ldcg(p.wordlocal + w0 + lane) : 0x7FFFFFFF;
-            const unsigned int le = __ballot_sync(0xffffffffu, lo <= need);
-            const int w = 31 - __clz(le);                  // last word whose prefix is <= need (word 0 always is)
-            if (lane == w) {
-                need -= lo;
-                unsigned int m = __ldcg(p.first + w0 + w);
-                for (; need > 0; --need) m &= m - 1;
-                p.state[f].istar = (cc * kChunkWords + w) * 32 + (__ffs(m) - 1);
-            }
-        }
-    }
+    __shared__ int s_lastframe;
     __threadfence();
     __syncthreads();
-    __shared__ int s_lastframe;
     if (threadIdx.x == 0) s_lastframe = (atomicAdd(&p.counters[0], 1) == p.nframes - 1);
     __syncthreads();
     if (!s_lastframe) return;
     __threadfence();
-    carry = 0;
+    int carry = 0;
     for (int b0 = 0; b0 < p.nframes; b0 += kBlock) {
         const int ff = b0 + threadIdx.x;
         const int m = ff < p.nframes ? __ldcg(&p.state[ff].m) : 0;
@@ -538,216 +611,347 @@ __device__ void frame_scan(const Pipe& p, const FrameDesc& fr, int f, int eff, i
         p.frame_voxel_offsets[p.nframes] = carry;
         if (p.voxel_num) *p.voxel_num = carry;         // single-frame form: M for the caller
         p.counters[0] = 0;
-        p.counters[1] = 0;
         p.counters[2] = 0;
     }
 }
 
-// grid (ceil(max chunks per frame / 8), B): one warp per chunk, one lane per 32-point word.
-// first = cand & ~lost; per-word and per-chunk counts; the block that finishes a frame's last
-// chunk runs the frame-level scan.  Clears the lost words it read (clean for the next call).
-__global__ void __launch_bounds__(kBlock, 8) k_verify(const Pipe p)
+// The break cut-off: the point that would open voxel #cap is the (cap - cut_base)-th first
+// occurrence of chunk cc.  One warp: 32 words, one per lane.
+__device__ __forceinline__ int find_istar(const Pipe& p, const FrameDesc& fr, int cc, int need, int nwords)
+{
+    const int lane = threadIdx.x & 31;
+    const int w = cc * kChunkWords + lane;
+    unsigned int fw = 0;
+    if (w < nwords) fw = __ldcg(p.cand + fr.word_off + w) & ~__ldcg(p.lost + fr.word_off + w);
+    int tot;
+    const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
+    const unsigned int le = __ballot_sync(0xffffffffu, ex <= need);
+    const int wl = 31 - __clz(le);                  // last word whose prefix is <= need (lane 0 always is)
+    int r = 0;
+    if (lane == wl) {
+        unsigned int m = fw;
+        for (int k = need - ex; k > 0; --k) m &= m - 1;
+        r = w * 32 + (__ffs(m) - 1);
+    }
+    return __shfl_sync(0xffffffffu, r, wl);
+}
+
+// Frames of more than kScanSmemChunks chunks (> 4 M points): one block per frame scans the chunk
+// counts into chunkbase[] and publishes the frame's results; k_mid<true> reads them from there.
+__global__ void __launch_bounds__(kBlock) k_scan_big(const __grid_constant__ Pipe p)
 {
     __shared__ int sm[kWarps + 1];
-    __shared__ int s_last;
-    pdl_prologue();
-    const int f = blockIdx.y;
-    const FrameDesc fr = p.frames[f];
-    const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));   // prefix that went through k_insert
-    const int nchunks = (eff + kChunk - 1) / kChunk;
-    const int c0 = blockIdx.x * kWarps;
-    {
-        // Every block of the frame also empties its share of the frame's bucket rows (T <= 8:
-        // the sorted chain needs them empty) or voxel counters (larger T), right before k_slot
-        // fills them: whole sectors, normal stores, so k_slot's atomics find the lines in the L2.
-        const bool chain = p.T <= kChainMaxT;
-        int* base = chain ? p.bucket + (size_t)f * p.cap * p.T : p.cnt + (size_t)f * p.cap;
-        const int rows = min(p.cap, fr.n);                  // a frame of n points opens at most n voxels
-        const int total = chain ? rows * p.T : rows;
-        const int per = (total + gridDim.x - 1) / gridDim.x;
-        const int lo = blockIdx.x * per, hi = min(total, lo + per);
-        const int fill = chain ? kEmptyIdx : 0;
-        if (hi > lo) {
-            // scalar head up to a 16-byte boundary, 16-byte stores, scalar tail
-            int* b0 = base + lo;
-            const int n = hi - lo;
-            const int head = min(n, (int)(((16u - (unsigned)((uintptr_t)b0 & 15u)) & 15u) >> 2));
-            if ((int)threadIdx.x < head) b0[threadIdx.x] = fill;
-            int4* b4 = reinterpret_cast<int4*>(b0 + head);
-            const int n4 = (n - head) >> 2;
-            const int4 f4 = make_int4(fill, fill, fill, fill);
-            for (int j = threadIdx.x; j < n4; j += kBlock) b4[j] = f4;
-            const int t0 = head + n4 * 4;
-            if ((int)threadIdx.x < n - t0) b0[t0 + threadIdx.x] = fill;
-        }
-    }
-    if (c0 >= nchunks && !(eff == 0 && blockIdx.x == 0)) return;
-    const int nwords = (eff + 31) / 32;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int c = c0 + wid;
-    if (c < nchunks) {
-        const int w = c * kChunkWords + lane;
-        unsigned int fw = 0;
-        if (w < nwords) {
-            const unsigned int lw = __ldcg(p.lost + fr.word_off + w);
-            fw = __ldcg(p.cand + fr.word_off + w) & ~lw;
-            if (lw) p.lost[fr.word_off + w] = 0u;
-            // points past the inserted prefix carry no bits: cand words are written whole by k_insert
-        }
+    __shared__ int s_cut[2];
+    const int f = blockIdx.x;
+    const FrameDesc fr = frame_desc(p, f);
+    const int eff = min(fr.n, __ldcg(&p.state[f].n_eff));
+    const int nch = (eff + kChunk - 1) / kChunk, nwords = (eff + 31) / 32;
+    int* cb = p.chunkbase + fr.chunk_off;
+    if (threadIdx.x == 0) s_cut[0] = -1;
+    __syncthreads();
+    int carry = 0;
+    for (int b0 = 0; b0 < nch; b0 += kBlock) {
+        const int c = b0 + threadIdx.x;
+        const int v = c < nch ? (int)(__ldcg(p.chunkstat + fr.chunk_off + c) & 0xFFFFu) : 0;
         int tot;
-        const int ex = warp_exclusive_scan(__popc(fw), lane, &tot);
-        if (w < nwords) {
-            p.first[fr.word_off + w] = fw;
-            p.wordlocal[fr.word_off + w] = ex;
+        const int ex = carry + block_exclusive_scan(v, &tot, sm);
+        if (c < nch) {
+            cb[c] = ex;
+            if (ex <= p.cap && p.cap < ex + v) { s_cut[0] = c; s_cut[1] = ex; }   // at most one thread
         }
-        if (lane == 0) p.chunkbase[fr.chunk_off + c] = tot;
+        carry += tot;
     }
-    // last chunk of the frame -> frame-level scan
-    __threadfence();
     __syncthreads();
+    const int total = carry;
+    const bool cut = !p.overflow_continue && total > p.cap;
+    int istar = eff;
+    if (cut && threadIdx.x < 32) istar = find_istar(p, fr, s_cut[0], p.cap - s_cut[1], nwords);
     if (threadIdx.x == 0) {
-        const int mine = eff == 0 ? 1 : min(kWarps, nchunks - c0);
-        s_last = (atomicAdd(&p.state[f].done_verify, mine) + mine == max(nchunks, 1));
+        FrameState* st = p.state + f;
+        st->total = total;
+        st->m = min(total, p.cap);
+        st->istar = istar;
+        st->n_done = eff;
+        st->rows = 0;
     }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    frame_scan(p, fr, f, eff, sm);
+    frames_done(p, sm);
 }
 
-// ---------------------------------------------------------------- k_slot
-// Rare path of k_slot: the first point a point recorded at insert time was displaced later
-// (chunks of one cell finishing out of order): find the cell's entry in the table.
-__device__ __forceinline__ unsigned int refind_first(const Pipe& p, const FrameDesc& fr, int i)
+// ---------------------------------------------------------------- k_mid
+// Voxel number of point fi if it is a first point = number of first points before it in the frame:
+// chunk prefix + candidate counts of the units before its unit + bits before it in its unit,
+// minus the displaced candidates before it (only chunks that have any: per-unit counts + the
+// unit's own `lost` words).  -1 if fi is not a first point (it was displaced after it was recorded).
+template <bool BIG>
+__device__ __forceinline__ int rank_of(const Pipe& p, const FrameDesc& fr, unsigned int fi, const int* s_pre,
+                                       const unsigned short* s_lost)
 {
-    float x, y, z;
-    load_xyz(p, fr, i, x, y, z);
-    const unsigned int cell = (unsigned)cell_of(p.g, x, y, z);
-    const unsigned long long* tbl = p.table + fr.tbl_off;
-    unsigned int hh = fr.tbl_shift < 0 ? cell : hash_cell(cell, fr.tbl_shift);
-    unsigned long long e = __ldcg(tbl + hh);
-    while ((unsigned)(e >> 32) != cell) {
-        hh = (hh + 1) & fr.tbl_mask;
-        e = __ldcg(tbl + hh);
+    const int c = (int)(fi >> 10), u = (int)(fi >> 7) & 7, wq = (int)(fi >> 5) & 3, b = (int)fi & 31;
+    const uint2 u8 = __ldg(reinterpret_cast<const uint2*>(p.unit8 + (size_t)(fr.chunk_off + c) * kWarps));
+    const uint4 cw = __ldg(reinterpret_cast<const uint4*>(p.cand + fr.word_off + c * kChunkWords + u * kPts));
+    int r, nlost;
+    if (BIG) {
+        r = __ldg(p.chunkbase + fr.chunk_off + c);
+        nlost = (int)(__ldcg(p.chunkstat + fr.chunk_off + c) >> 16);
+    } else {
+        r = s_pre[c];
+        nlost = s_lost[c];
     }
-    return (unsigned)e;
+    // bytes 0 .. u-1 of the eight unit counts
+    const unsigned int mlo = u >= 4 ? 0xFFFFFFFFu : ((1u << (8 * u)) - 1u);
+    const unsigned int mhi = u <= 4 ? 0u : ((1u << (8 * (u - 4))) - 1u);
+    r += (int)__vsadu4(u8.x & mlo, 0u) + (int)__vsadu4(u8.y & mhi, 0u);
+    const unsigned int bit = 1u << b, below = bit - 1u;
+    const unsigned int m0 = wq > 0 ? 0xFFFFFFFFu : below, m1 = wq > 1 ? 0xFFFFFFFFu : (wq == 1 ? below : 0u),
+                       m2 = wq > 2 ? 0xFFFFFFFFu : (wq == 2 ? below : 0u), m3 = wq == 3 ? below : 0u;
+    r += __popc(cw.x & m0) + __popc(cw.y & m1) + __popc(cw.z & m2) + __popc(cw.w & m3);
+    unsigned int mine = wq == 0 ? cw.x : (wq == 1 ? cw.y : (wq == 2 ? cw.z : cw.w));
+    if (nlost) {
+        const uint2 l8 = __ldcg(reinterpret_cast<const uint2*>(p.lunit32 + (size_t)(fr.chunk_off + c) * 2));
+        const uint4 lw = __ldcg(reinterpret_cast<const uint4*>(p.lost + fr.word_off + c * kChunkWords + u * kPts));
+        r -= (int)__vsadu4(l8.x & mlo, 0u) + (int)__vsadu4(l8.y & mhi, 0u);
+        r -= __popc(lw.x & m0) + __popc(lw.y & m1) + __popc(lw.z & m2) + __popc(lw.w & m3);
+        mine &= ~(wq == 0 ? lw.x : (wq == 1 ? lw.y : (wq == 2 ? lw.z : lw.w)));
+    }
+    return (mine & bit) ? r : -1;
 }
 
-// grid (gx, B): block x of frame f walks chunks x, x+gx, ... below the break
-// cut-off, so the launch carries no blocks that only exit.  Same round structure as
-// k_insert: per round one atomic per point in flight.
-__global__ void __launch_bounds__(kBlock, 8) k_slot(const Pipe p)
+// Extras {point index, table slot of its cell}: the cell's entry holds its first point; that
+// point's voxel number is the extra's voxel; the extra takes its slot among the voxel's other points.
+// (In break mode extras behind the cut-off may get a slot too: they are the largest indices of their
+// voxel, never push a smaller one out, and the gather drops them.)  Two extras per lane at a time, so
+// that their lookups and their first atomics are in flight together: the pass is a chain of dependent
+// L2 / DRAM round trips, not a throughput problem.
+template <bool BIG>
+__device__ __forceinline__ int extra_rank(const Pipe& p, const FrameDesc& fr, int2 e, const int* s_pre,
+                                          const unsigned short* s_lost)
 {
+    const unsigned int fi = (unsigned int)__ldcg(p.table + fr.tbl_off + (unsigned int)e.y);
+    return rank_of<BIG>(p, fr, fi, s_pre, s_lost);
+}
+
+__device__ __forceinline__ void place_extra(const Pipe& p, int f, int rank, int i, int first_old, bool have_first)
+{
+    const int T1 = p.T - 1;
+    const size_t g = (size_t)f * p.cap + rank;
+    if (p.T <= kChainMaxT) {
+        // sorted insertion over the voxel's T-1 slots: slot j ends up holding the (j+1)-th
+        // smallest index among the voxel's extras (the atomic on slot 0 may have been issued already)
+        int* b = p.bucket + g * T1;
+        int cur = i;
+        for (int s = 0; s < T1; ++s) {
+            const int old = (s == 0 && have_first) ? first_old : atomicMin(b + s, cur);
+            if (old == kEmptyIdx) break;
+            cur = max(old, cur);
+        }
+    } else {
+        const int k = atomicAdd(p.cnt + g, 1);
+        if (k < T1) {
+            p.bucket[g * T1 + k] = i;
+        } else {
+            const int o = atomicAdd(&p.counters[1], 1);
+            if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
+        }
+    }
+}
+
+template <bool BIG>
+__device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, int f, bool v0, int2 e0, bool v1, int2 e1,
+                                          const int* s_pre, const unsigned short* s_lost)
+{
+    int r0 = v0 ? extra_rank<BIG>(p, fr, e0, s_pre, s_lost) : 0x7FFFFFFF;
+    int r1 = v1 ? extra_rank<BIG>(p, fr, e1, s_pre, s_lost) : 0x7FFFFFFF;
+    const bool chain = p.T <= kChainMaxT;
+    int o0 = 0, o1 = 0;
+    if (chain) {
+        const int T1 = p.T - 1;
+        if ((unsigned)r0 < (unsigned)p.cap) o0 = atomicMin(p.bucket + ((size_t)f * p.cap + r0) * T1, e0.x);
+        if ((unsigned)r1 < (unsigned)p.cap) o1 = atomicMin(p.bucket + ((size_t)f * p.cap + r1) * T1, e1.x);
+    }
+    if ((unsigned)r0 < (unsigned)p.cap) place_extra(p, f, r0, e0.x, o0, chain);
+    if ((unsigned)r1 < (unsigned)p.cap) place_extra(p, f, r1, e1.x, o1, chain);
+}
+
+// grid (gx + 1, B); dynamic smem (not BIG): (max chunks per frame + 1) x 10 bytes.  Every block of
+// frame f scans the frame's chunk counts in shared memory (<= 4096 ints: cheaper than a kernel boundary
+// and a last-block chain).  Then the blocks of a frame split by role, so that the three latency chains
+// run side by side instead of one after the other:
+//   * the LAST block only publishes the frame's results (and, for the last frame to get there, the
+//     voxel offsets of the call)
+//   * blocks [0, n2): one warp per chunk: the chunk's first points get their voxel number from the
+//     bitmaps and are written to vfirst; the first point of would-be voxel #cap is the break cut-off i*
+//   * blocks [n2, gx): the frame's extras, spread evenly over their warps (the chunks' lists are very
+//     uneven: late chunks hold most of them): voxel number of the recorded first point -> slot
+// (one block per frame besides the publisher does both jobs)
+template <bool BIG>
+__global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe p, int smem_chunks, int n2)
+{
+    extern __shared__ int s_dyn[];
+    __shared__ int sm[kWarps + 1];
+    __shared__ int s_cut;
     pdl_prologue();
     const int f = blockIdx.y;
-    const FrameDesc fr = p.frames[f];
-    const int lim = min(p.state[f].n_done, p.state[f].istar);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {   // k_insert's per-frame counters, for the next call
-        p.state[f].ticket = 0ull;
-        p.state[f].cleared = 0;
-        p.state[f].n_eff = 0x7FFFFFFF;
+    const FrameDesc fr = frame_desc(p, f);
+    FrameState* st = p.state + f;
+    int* s_pre = s_dyn;                                  // [smem_chunks] exclusive prefix of the first-point counts
+    int* s_epre = s_dyn + smem_chunks;                   // [smem_chunks + 1] exclusive prefix of the extras counts
+    unsigned short* s_lost = reinterpret_cast<unsigned short*>(s_dyn + 2 * smem_chunks + 1);
+    const int cap = p.cap;
+    const bool brk = !p.overflow_continue;
+    const int gx = gridDim.x - 1;
+    const bool publisher = (int)blockIdx.x == gx;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    // n2 == 0: every block does both jobs (numbering, then extras); else blocks [0, n2) number, [n2, gx) place
+    const bool role2 = n2 == 0 || (int)blockIdx.x < n2, role3 = (n2 == 0 || (int)blockIdx.x >= n2) && !publisher;
+    const int nw2 = (n2 == 0 ? gx : n2) * kWarps, nw3 = (n2 == 0 ? gx : gx - n2) * kWarps;
+    const int w2 = blockIdx.x * kWarps + wid, w3 = (n2 == 0 ? (int)blockIdx.x : (int)blockIdx.x - n2) * kWarps + wid;
+#if BVX_ABL == 3
+    if (!publisher) return;
+#endif
+    // the bitmap words of the first chunk this warp numbers are fetched before anything else
+    unsigned int pf_c = 0, pf_l = 0;
+    if (!BIG && role2 && !publisher && w2 < fr.nchunks) {
+        const int w = w2 * kChunkWords + lane;
+        if (w < fr.nwords) { pf_c = __ldcg(p.cand + fr.word_off + w); pf_l = __ldcg(p.lost + fr.word_off + w); }
     }
-    const int T = p.T;
-    for (int base = blockIdx.x * kChunk; base < lim; base += gridDim.x * kChunk) {
-        int sl[kPts];
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) {
-            const int i = base + k * kBlock + threadIdx.x;
-            sl[k] = i < lim ? __ldg(p.slot + fr.pt_off + i) : -1;   // first point of my cell, as seen at insert
+    int total, eff, nch, cut_chunk;
+    if (BIG) {
+        eff = __ldcg(&st->n_done);
+        nch = (eff + kChunk - 1) / kChunk;
+        total = __ldcg(&st->total);
+        cut_chunk = total > cap ? (brk ? __ldcg(&st->istar) / kChunk : nch - 1) : nch - 1;
+        if (publisher) return;
+    } else {
+        // thread t scans chunks [t*per, (t+1)*per); the loads do not wait for n_eff
+        const int per = (fr.nchunks + kBlock - 1) / kBlock;
+        const int c0 = min(fr.nchunks, (int)threadIdx.x * per), c1 = min(fr.nchunks, c0 + per);
+        eff = min(fr.n, __ldcg(&st->n_eff));     // prefix that went through k_insert
+        int sum = 0, esum = 0;
+        for (int c = c0; c < c1; ++c) {
+            const unsigned int v = __ldcg(p.chunkstat + fr.chunk_off + c);
+            const int ne = __ldcg(p.extn + fr.chunk_off + c);
+            const bool in = c * kChunk < eff;           // (a chunk behind the prefix: zero count, stale list length)
+            s_pre[c] = (int)(v & 0xFFFFu);
+            s_epre[c] = in ? ne : 0;
+            s_lost[c] = (unsigned short)(v >> 16);
+            sum += (int)(v & 0xFFFFu);
+            esum += in ? ne : 0;
         }
-        // voxel number = rank of the recorded first point among the frame's first points: three
-        // small lookups, issued unconditionally (index 0 for out-of-range points) for all four points
-        unsigned int fw[kPts];
-        int rank[kPts];
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) {
-            const unsigned int fidx = (unsigned)max(sl[k], 0);
-            const int w = fr.word_off + (int)(fidx >> 5);
-            fw[k] = __ldg(p.first + w);
-            rank[k] = __ldg(p.chunkbase + fr.chunk_off + (int)(fidx / kChunk)) + __ldg(p.wordlocal + w);
+        nch = (eff + kChunk - 1) / kChunk;
+        if (threadIdx.x == 0) s_cut = nch - 1;
+        int etotal;
+        int eex = block_exclusive_scan(esum, &etotal, sm);
+        int ex = block_exclusive_scan(sum, &total, sm);
+        for (int c = c0; c < c1; ++c) {
+            const int v = s_pre[c], ne = s_epre[c];
+            s_pre[c] = ex;
+            s_epre[c] = eex;
+            if (ex <= cap && cap < ex + v) s_cut = c;   // at most one thread: the chunk that holds first point #cap
+            ex += v;
+            eex += ne;
         }
-        unsigned int stale = 0;
-#pragma unroll
-        for (int k = 0; k < kPts; ++k) {
-            const unsigned int fidx = (unsigned)max(sl[k], 0);
-            const unsigned int bit = (fw[k] >> (fidx & 31)) & 1u;
-            if (sl[k] >= 0 && !bit) stale |= 1u << k;
-            rank[k] = sl[k] >= 0 ? rank[k] + __popc(fw[k] & ((1u << (fidx & 31)) - 1u)) : 0x7FFFFFFF;
-        }
-        if (stale) {
-            // rare: the recorded point lost its place later; look the cell up in the table
-#pragma unroll
-            for (int k = 0; k < kPts; ++k) {
-                if (!(stale & (1u << k))) continue;
-                const unsigned int fidx = refind_first(p, fr, base + k * kBlock + threadIdx.x);
-                sl[k] = (int)fidx;
-                const int w = fr.word_off + (int)(fidx >> 5);
-                rank[k] = __ldg(p.chunkbase + fr.chunk_off + (int)(fidx / kChunk)) + __ldg(p.wordlocal + w) +
-                          __popc(__ldg(p.first + w) & ((1u << (fidx & 31)) - 1u));
+        if (threadIdx.x == 0) s_epre[fr.nchunks] = etotal;
+        __syncthreads();
+        cut_chunk = s_cut;
+        if (publisher) {
+            if (threadIdx.x == 0) {
+                st->total = total;
+                st->m = min(total, cap);
+                if (!(brk && total > cap)) st->istar = eff;      // else: written by the warp that meets first point #cap
+                st->n_done = eff;
+                st->rows = 0;
             }
+            frames_done(p, sm);
+            return;
         }
-        // rank >= cap: out of range, cut off, or (continue mode) a voxel beyond the cap
-        if (T <= kChainMaxT) {
-            // Slot 0 belongs to the voxel's first point (the smallest index by definition): a plain
-            // store into the row k_verify just emptied, no round trip.  The other points go through a
-            // sorted insertion over slots 1 .. T-1: slot j ends up holding the (j+1)-th smallest index.
-            int cur[kPts];
-            int* b[kPts];
-            unsigned int active = 0;
-#pragma unroll
-            for (int k = 0; k < kPts; ++k) {
-                cur[k] = base + k * kBlock + threadIdx.x;
-                b[k] = p.bucket + ((size_t)f * p.cap + (rank[k] < p.cap ? rank[k] : 0)) * T;
-                if (rank[k] < p.cap) {
-                    if (sl[k] == cur[k]) b[k][0] = cur[k];
-                    else active |= 1u << k;
-                }
+    }
+#if BVX_ABL == 4
+    return;
+#endif
+    const int nwords = (eff + 31) / 32;
+    const int nlim = (brk && total > cap) ? cut_chunk + 1 : nch;   // chunks that can hold anything that is kept
+    if (role2) {
+        for (int c = w2; c < nlim; c += nw2) {
+            const int cidx = fr.chunk_off + c;
+            int pre, nlost;
+            if (BIG) {
+                pre = __ldg(p.chunkbase + cidx);
+                nlost = (int)(__ldcg(p.chunkstat + cidx) >> 16);
+            } else {
+                pre = s_pre[c];
+                nlost = s_lost[c];
             }
-            for (int j = 1; j < T && active; ++j) {
-                int old[kPts];
-#pragma unroll
-                for (int k = 0; k < kPts; ++k)
-                    old[k] = (active & (1u << k)) ? atomicMin(b[k] + j, cur[k]) : 0;
-#pragma unroll
-                for (int k = 0; k < kPts; ++k) {
-                    if (active & (1u << k)) {
-                        if (old[k] == kEmptyIdx) active &= ~(1u << k);
-                        else cur[k] = max(old[k], cur[k]);
+            if (pre <= cap) {
+                // first points of the chunk -> vfirst[voxel number]
+                const int w = c * kChunkWords + lane;
+                unsigned int fw = 0;
+                if (w < nwords) {
+                    if (!BIG && c == w2) {
+                        fw = pf_c & ~pf_l;
+                    } else {
+                        fw = __ldcg(p.cand + fr.word_off + w);
+                        if (nlost) fw &= ~__ldcg(p.lost + fr.word_off + w);
                     }
                 }
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < kPts; ++k) {
-                if (rank[k] >= p.cap) continue;
-                const int i = base + k * kBlock + threadIdx.x;
-                const size_t g = (size_t)f * p.cap + rank[k];
-                const int c = atomicAdd(p.cnt + g, 1);
-                if (c < T) {
-                    p.bucket[g * T + c] = i;
-                } else {
-                    const int o = atomicAdd(&p.counters[1], 1);
-                    if (o < p.ovf_cap) p.ovf[o] = make_int2((int)g, i);
+                int tot;
+                int v = pre + warp_exclusive_scan(__popc(fw), lane, &tot);
+                int* vf = p.vfirst + (size_t)f * cap;
+                while (fw && v <= cap) {
+                    const int i = w * 32 + (__ffs(fw) - 1);
+                    if (v < cap) vf[v] = i;
+                    else if (brk && !BIG) st->istar = i;       // the point that would open voxel #cap
+                    fw &= fw - 1;
+                    ++v;
                 }
             }
+            if (BIG && p.T > 1) {
+                // (frames of > 4 M points) the chunk's own extras, by the same warp
+                const int ne = __ldcg(p.extn + cidx);
+                const int2* ext = p.extras + (size_t)cidx * kChunk;
+                for (int j = lane; j < ne; j += 32)
+                    place_two<BIG>(p, fr, f, true, __ldcs(ext + j), false, make_int2(0, 0), s_pre, s_lost);
+            }
         }
+    }
+    if (BIG || p.T <= 1 || !role3) return;
+#if BVX_ABL == 1
+    return;
+#endif
+    // extras of chunks [0, nlim), flattened: item g of the frame belongs to the chunk c with
+    // s_epre[c] <= g < s_epre[c + 1]; consecutive lanes take consecutive items, two per lane at a time
+    const int E = s_epre[nlim];
+    auto fetch = [&](int g) {
+        int lo = 0, hi = nlim - 1;             // largest c with s_epre[c] <= g
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_epre[mid] <= g) lo = mid; else hi = mid - 1;
+        }
+        return __ldcs(p.extras + (size_t)(fr.chunk_off + lo) * kChunk + (g - s_epre[lo]));
+    };
+    for (int g0 = w3 * 64; g0 < E; g0 += nw3 * 64) {
+        const int ga = g0 + lane, gb = g0 + 32 + lane;
+        const bool va = ga < E, vb = gb < E;
+        const int2 ea = va ? fetch(ga) : make_int2(0, 0);
+        const int2 eb = vb ? fetch(gb) : make_int2(0, 0);
+        place_two<BIG>(p, fr, f, va, ea, vb, eb, s_pre, s_lost);
     }
 }
 
 // ---------------------------------------------------------------- k_overflow
-// Large-T path: a crowded voxel's bucket holds T arbitrary members; every other
-// member is offered here and the bucket keeps the T smallest indices.
-__global__ void __launch_bounds__(kBlock) k_overflow(const Pipe p)
+// Large-T path: a crowded voxel's bucket holds T-1 arbitrary extras; every other
+// extra is offered here and the bucket keeps the T-1 smallest indices.
+__global__ void __launch_bounds__(kBlock) k_overflow(const __grid_constant__ Pipe p)
 {
     const int n = min(((volatile int*)p.counters)[1], p.ovf_cap);
+    const int T1 = p.T - 1;
     for (int j = blockIdx.x * kBlock + threadIdx.x; j < n; j += gridDim.x * kBlock) {
         const int2 it = p.ovf[j];
-        int* b = p.bucket + (size_t)it.x * p.T;
+        int* b = p.bucket + (size_t)it.x * T1;
         int mx = 0;
-        for (int k = 0; k < p.T; ++k) mx = max(mx, __ldcg(b + k));
-        if (it.y > mx) continue;  // entries only decrease: cannot be among the T smallest
+        for (int k = 0; k < T1; ++k) mx = max(mx, __ldcg(b + k));
+        if (it.y > mx) continue;  // entries only decrease: cannot be among the T-1 smallest
         int cur = it.y;
-        for (int k = 0; k < p.T; ++k) {
+        for (int k = 0; k < T1; ++k) {
             const int old = atomicMin(b + k, cur);
             cur = max(old, cur);
         }
@@ -779,6 +983,29 @@ __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, 
     }
 }
 
+// Every gather block first does its share of putting the frame's per-call structures back into
+// their between-calls state (the gather is the call's last kernel): displaced-candidate bits and
+// chunk counters to zero, k_insert's per-frame counters to their start values.
+__device__ __forceinline__ void tidy_frame(const Pipe& p, const FrameDesc& fr, int f)
+{
+    FrameState* st = p.state + f;
+    const int eff = st->n_done;
+    const int nwords = (eff + 31) / 32, nch = (eff + kChunk - 1) / kChunk;
+    const int stride = gridDim.x * kBlock;
+    for (int w = blockIdx.x * kBlock + threadIdx.x; w < nwords; w += stride) p.lost[fr.word_off + w] = 0u;
+    for (int c = blockIdx.x * kBlock + threadIdx.x; c < nch; c += stride) {
+        p.chunkstat[fr.chunk_off + c] = 0u;
+        reinterpret_cast<uint2*>(p.lunit32)[fr.chunk_off + c] = make_uint2(0u, 0u);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->ticket = 0ull;
+        st->cleared = 0;
+        st->clear_claim = 0;
+        st->n_eff = 0x7FFFFFFF;
+        if (f == 0) p.counters[1] = 0;
+    }
+}
+
 __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int cell)
 {
     const int gx = p.g.gs[0], gy = p.g.gs[1];
@@ -792,18 +1019,19 @@ __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int 
     }
 }
 
-// Fast path: T <= 8 (bucket already sorted by the atomicMin chain), 4 floats per
+// Fast path: T <= 8 (extras already sorted by the atomicMin chain), 4 floats per
 // point, 16-byte aligned rows.  One thread per voxel: T independent row loads in
 // flight, mean and coordinates from registers; the voxel rows go through a
 // per-warp shared-memory transpose so the [M, T, 4] store is fully coalesced.
 // grid (tiles + reset chunks, B); dynamic smem = kWarps * 32 * T * 16 bytes.
 template <int T>
-__global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles)
+__global__ void __launch_bounds__(kBlock) k_gather_small(const __grid_constant__ Pipe p, int tiles)
 {
     extern __shared__ float4 smem_v[];
     pdl_prologue();
     const int f = blockIdx.y;
-    const FrameDesc fr = p.frames[f];
+    const FrameDesc fr = frame_desc(p, f);
+    tidy_frame(p, fr, f);
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * kBlock;
@@ -813,18 +1041,36 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
     const bool live = v < mf;
     const size_t gbase = (size_t)p.frame_voxel_offsets[f];
     int idx[T];
-    int* gb = p.bucket + ((size_t)f * p.cap + v) * T;
+    idx[0] = live ? __ldcs(p.vfirst + (size_t)f * p.cap + v) : kEmptyIdx;
+    if (T > 1) {
+        // the voxel's other points, ascending; a row that held any is put back to empty for the next
+        // call.  Break mode: entries behind the cut-off i* (a suffix of the row) are dropped here.
+        const int istar = p.state[f].istar;
+        int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
+        if (T == 5) {
+            int4 e = make_int4(kEmptyIdx, kEmptyIdx, kEmptyIdx, kEmptyIdx);
+            if (live) e = *reinterpret_cast<const int4*>(gb);
+            if (e.x != kEmptyIdx)
+                *reinterpret_cast<int4*>(gb) = make_int4(kEmptyIdx, kEmptyIdx, kEmptyIdx, kEmptyIdx);
+            idx[1 % T] = e.x < istar ? e.x : kEmptyIdx; idx[2 % T] = e.y < istar ? e.y : kEmptyIdx;
+            idx[3 % T] = e.z < istar ? e.z : kEmptyIdx; idx[4 % T] = e.w < istar ? e.w : kEmptyIdx;
+        } else {
 #pragma unroll
-    for (int s = 0; s < T; ++s) {
-        idx[s] = live ? gb[s] : kEmptyIdx;
+            for (int s = 1; s < T; ++s) {
+                const int raw = live ? gb[s - 1] : kEmptyIdx;
+                if (raw != kEmptyIdx) gb[s - 1] = kEmptyIdx;
+                idx[s] = raw < istar ? raw : kEmptyIdx;
+            }
+        }
     }
+    const float4* rows = reinterpret_cast<const float4*>(plain_rows(p, fr));
     float4 row[T];
     int nvalid = 0;
 #pragma unroll
     for (int s = 0; s < T; ++s) {
         row[s] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (idx[s] != kEmptyIdx) {
-            row[s] = __ldg(reinterpret_cast<const float4*>(fr.pts0) + idx[s]);
+            row[s] = __ldg(rows + idx[s]);
             ++nvalid;
         }
     }
@@ -851,7 +1097,7 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
     }
     if (p.crow) {
         // compact rows for the host form: the tile reserves a range for its kept points, each voxel
-        // writes its rows (slots 0 .. nvalid-1 of the sorted bucket) at its prefix inside the range
+        // writes its rows (slots 0 .. nvalid-1) at its prefix inside the range
         __shared__ int s_scan[kWarps + 1];
         __shared__ int s_base;
         int tot;
@@ -892,53 +1138,73 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const Pipe p, int tiles
     }
 }
 
-// General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T bucket
-// entries) staged through shared memory; entries are rank-sorted in shared memory
+// General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T entries: the first
+// point + T-1 bucket slots) staged through shared memory; entries are rank-sorted in shared memory
 // (the large-T bucket is unordered).
-// grid (tiles + reset chunks, B); dynamic smem: round4(E) + round4(vt) ints + E*f_out floats, E = vt*T.
-__global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int vt)
+// grid (tiles + reset chunks, B); dynamic smem: round4(E) + 2*round4(vt) ints + E*f_out floats, E = vt*T.
+__global__ void __launch_bounds__(kBlock) k_gather(const __grid_constant__ Pipe p, int tiles, int vt)
 {
     extern __shared__ int smem_i[];
     pdl_prologue();
     const int f = blockIdx.y;
-    const FrameDesc fr = p.frames[f];
+    const FrameDesc fr = frame_desc(p, f);
+    tidy_frame(p, fr, f);
     if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * vt;
     if (v0 >= mf) return;
-    const int T = p.T, F = p.f_out;
+    const int T = p.T, T1 = p.T - 1, F = p.f_out;
     const int nv = min(vt, mf - v0);
     const int E = nv * T;
     int* sidx = smem_i;
     int* scnt = smem_i + ((vt * T + 3) & ~3);                  // live entries per voxel
-    float* srow = reinterpret_cast<float*>(scnt + ((vt + 3) & ~3));
-    int* gb = p.bucket + ((size_t)f * p.cap + v0) * T;
-    for (int e = threadIdx.x; e < E; e += kBlock) sidx[e] = gb[e];
-    if (T > kChainMaxT) {
-        // count + bucket path: the counter says how many points the voxel saw; the live
-        // entries are the first min(count, T) positions of its bucket, in arrival order
-        // (what lies behind them is left over from earlier calls)
-        for (int v = threadIdx.x; v < nv; v += kBlock)
-            scnt[v] = min(p.cnt[(size_t)f * p.cap + v0 + v], T);
-        __syncthreads();
-    } else {
-        __syncthreads();
-        for (int v = threadIdx.x; v < nv; v += kBlock) {
-            int c = 0;
-            for (int k = 0; k < T; ++k) c += (sidx[v * T + k] != kEmptyIdx);
-            scnt[v] = c;
-        }
-        __syncthreads();
+    float* srow = reinterpret_cast<float*>(scnt + 2 * ((vt + 3) & ~3));
+    const size_t g0 = (size_t)f * p.cap + v0;
+    int* gb = p.bucket + g0 * T1;
+    for (int e = threadIdx.x; e < E; e += kBlock) {
+        const int v = e / T, s = e - v * T;
+        sidx[e] = s == 0 ? __ldcs(p.vfirst + g0 + v) : gb[(size_t)v * T1 + s - 1];
     }
+    __syncthreads();
+    // scnt[v]: live entries (the first point + the extras the bucket holds); snv[v]: those kept, i.e.
+    // in front of the break cut-off i* -- they are the smallest indices of the voxel
+    int* snv = scnt + ((vt + 3) & ~3);
+    const int istar = p.state[f].istar;
+    if (T > kChainMaxT) {
+        // count + bucket path: the counter says how many extras the voxel saw; the live entries
+        // are the first min(count, T-1) positions of its bucket, in arrival order (what lies
+        // behind them is left over from earlier calls); the counter goes back to zero
+        for (int v = threadIdx.x; v < nv; v += kBlock) {
+            const int nl = 1 + min(p.cnt[g0 + v], T1);
+            p.cnt[g0 + v] = 0;
+            int c = 1;
+            for (int k = 1; k < nl; ++k) c += (sidx[v * T + k] < istar);
+            scnt[v] = nl;
+            snv[v] = c;
+        }
+    } else {
+        // chain path: slots 0 .. k-1 are filled in ascending order; they go back to empty
+        for (int v = threadIdx.x; v < nv; v += kBlock) {
+            int nl = 1, c = 1;
+            for (int k = 1; k < T; ++k) {
+                const int e = sidx[v * T + k];
+                if (e != kEmptyIdx) { ++nl; gb[(size_t)v * T1 + k - 1] = kEmptyIdx; }
+                c += (e < istar);
+            }
+            scnt[v] = nl;
+            snv[v] = c;
+        }
+    }
+    __syncthreads();
     const size_t gout = (size_t)p.frame_voxel_offsets[f] + v0;
     for (int e = threadIdx.x; e < E; e += kBlock) {
         const int v = e / T, s = e - v * T;
         const int my = sidx[e];
-        const int nvalid = scnt[v];
-        if (s < nvalid) {               // (T <= 8: the chain fills slots 0 .. nvalid-1 in order)
+        const int nlive = scnt[v], nvalid = snv[v];
+        if (s < nlive && (s == 0 || my < istar)) {
             const int* vb = sidx + v * T;
             int r = 0;
-            for (int k = 0; k < nvalid; ++k) r += (vb[k] < my);   // slot = rank of the index in the voxel
+            for (int k = 0; k < nlive; ++k) r += (vb[k] < my);    // slot = rank of the index in the voxel
             float* dst = srow + (size_t)(v * T + r) * F;
             fetch_row(p, fr, my, dst);
             if (p.idx_out) p.idx_out[(gout + v) * T + r] = my;
@@ -967,7 +1233,7 @@ __global__ void __launch_bounds__(kBlock) k_gather(const Pipe p, int tiles, int 
         const int C = p.mean_c;
         for (int k = threadIdx.x; k < nv * C; k += kBlock) {
             const int v = k / C, c = k - v * C;
-            const int nvalid = scnt[v];
+            const int nvalid = snv[v];
             float s = 0.0f;
             for (int j = 0; j < T; ++j) s = __fadd_rn(s, srow[(size_t)(v * T + j) * F + c]);
             p.mean_out[(gout + v) * C + c] = __fdiv_rn(s, (float)nvalid);

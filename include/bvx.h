@@ -324,8 +324,9 @@ int bvx_fused_get_anchors_area(const float* dense_map, int32_t ny, int32_t nx,
 /* Optional per-kernel device timing: CUDA events are recorded on the call's
  * stream around every kernel of the pipeline while enabled.  bvx_profile_read
  * synchronises those events and returns accumulated milliseconds and launch
- * counts per kernel slot: 0 k_insert, 1 k_verify (+ rank scan), 3 k_slot,
- * 4 k_overflow, 5 k_gather (slots 2, 6, 7 unused). */
+ * counts per kernel slot: 0 k_insert, 1 k_mid (frame scan, voxel numbers,
+ * slots of the non-first points), 4 k_overflow, 5 k_gather (slots 2, 3, 6, 7
+ * unused). */
 #define BVX_PROFILE_SLOTS 8
 int bvx_profile_enable(bvx_handle* h, int32_t on);
 int bvx_profile_read(bvx_handle* h, double ms[BVX_PROFILE_SLOTS],

@@ -1,11 +1,12 @@
-"""Per-kernel device times of generate_batched on cfg4-shaped input (experiments)."""
+"""Per-kernel device times of generate_batched on cfg4-shaped input (experiments).
+usage: python tools/kprof.py [frames=64] [overflow=break] [steps=30]"""
 import importlib, os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pkg = importlib.import_module("3dobject_detection_temporal_b200")
 frames_n = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 overflow = sys.argv[2] if len(sys.argv) > 2 else "break"
-steps = 30
+steps = int(sys.argv[3]) if len(sys.argv) > 3 else 30
 c = pkg.synth.CONFIGS["cfg4"]
 frames = [pkg.synth.lidar_frame(c["n"], "kitti", i) for i in range(frames_n)]
 offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
@@ -28,5 +29,5 @@ for i in range(steps):
     gen.generate_batched(sets[i % 3], offs, mean_channels=4, padded=True, out=out)
 torch.cuda.synchronize()
 pr = gen.profile_read()
-print(f"frames={frames_n} {overflow} step={tot*1e3:.1f}us " +
-      " ".join(f"{k}={v[0]/v[1]*1e3:.1f}" for k, v in pr.items()))
+print(f"{os.environ.get('BVX_LIB', 'libbvx.so').split('/')[-1]} frames={frames_n} {overflow} step={tot*1e3:.1f}us " +
+      " ".join(f"{k}={v[0]/v[1]*1e3:.1f}" for k, v in pr.items()), flush=True)
