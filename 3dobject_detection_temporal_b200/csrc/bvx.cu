@@ -110,7 +110,6 @@ struct bvx_handle {
     unsigned int* lost = nullptr;
     unsigned char* unit8 = nullptr;
     unsigned int* chunkstat = nullptr;
-    unsigned int* lunit32 = nullptr;
     int2* extras = nullptr;
     int* extn = nullptr;
     int* chunkbase = nullptr;
@@ -287,7 +286,7 @@ extern "C" int bvx_destroy(bvx_handle* h)
 {
     if (!h) return BVX_OK;
     cudaSetDevice(h->device);
-    cudaFree(h->table); cudaFree(h->cand); cudaFree(h->lost); cudaFree(h->unit8); cudaFree(h->chunkstat); cudaFree(h->lunit32);
+    cudaFree(h->table); cudaFree(h->cand); cudaFree(h->lost); cudaFree(h->unit8); cudaFree(h->chunkstat);
     cudaFree(h->extras); cudaFree(h->extn); cudaFree(h->chunkbase); cudaFree(h->vfirst); cudaFree(h->bucket);
     cudaFree(h->cnt); cudaFree(h->ovf);
     cudaFree(h->counters); cudaFree(h->d_frames); cudaFree(h->d_segs); cudaFree(h->d_state);
@@ -360,6 +359,11 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
             volatile float r = 1.0f / cfg->voxel_size[j];
             h->grid.rvs[j] = std::isnormal((float)r) ? (float)r : std::nanf("");
         }
+        {
+            // margin of the divide-free cell index: 2^-21 (grid + 1), rounded up
+            const double m = ((double)gs[j] + 1.0) / 2097152.0;
+            h->grid.mg[j] = std::nextafterf((float)m, INFINITY);
+        }
         h->grid.gs[j] = (int)gs[j];
         h->grid.gsf[j] = (float)gs[j];
     }
@@ -382,11 +386,10 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if ((e = dalloc(h, &h->lost, (size_t)h->words_cap)) != cudaSuccess) return bail(e, "alloc lost");
     if ((e = cudaMemset(h->lost, 0, (size_t)h->words_cap * 4)) != cudaSuccess) return bail(e, "memset lost");
     h->chunks_cap = np / kChunk + 2 * nf + 8;
-    if ((e = dalloc(h, &h->unit8, (size_t)h->chunks_cap * kWarps)) != cudaSuccess) return bail(e, "alloc unit8");
+    if ((e = dalloc(h, &h->unit8, (size_t)h->chunks_cap * 16)) != cudaSuccess) return bail(e, "alloc unit8");
+    if ((e = cudaMemset(h->unit8, 0, (size_t)h->chunks_cap * 16)) != cudaSuccess) return bail(e, "memset unit8");
     if ((e = dalloc(h, &h->chunkstat, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkstat");
     if ((e = cudaMemset(h->chunkstat, 0, (size_t)h->chunks_cap * 4)) != cudaSuccess) return bail(e, "memset chunkstat");
-    if ((e = dalloc(h, &h->lunit32, (size_t)h->chunks_cap * 2)) != cudaSuccess) return bail(e, "alloc lunit32");
-    if ((e = cudaMemset(h->lunit32, 0, (size_t)h->chunks_cap * 8)) != cudaSuccess) return bail(e, "memset lunit32");
     if ((e = dalloc(h, &h->extras, (size_t)h->chunks_cap * kChunk)) != cudaSuccess) return bail(e, "alloc extras");
     if ((e = dalloc(h, &h->extn, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc extn");
     if ((e = dalloc(h, &h->chunkbase, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkbase");
@@ -445,7 +448,7 @@ struct FrameSpec {
 };
 
 // Chunk rows of k_insert = blocks of one frame in flight at a time (persistent; see run_pipeline).
-static int insert_rows_bound(int B) { return std::max(1, (148 * 8 + B - 1) / B); }
+static int insert_rows_bound(int B) { return std::max(1, (148 * BVX_INSERT_BLOCKS + B - 1) / B); }
 
 static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
                          int* max_n_out, bool* all_aligned)
@@ -679,7 +682,6 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     p.lost = h->lost;
     p.unit8 = h->unit8;
     p.chunkstat = h->chunkstat;
-    p.lunit32 = h->lunit32;
     p.extras = h->extras;
     p.extn = h->extn;
     p.chunkbase = h->chunkbase;
@@ -742,10 +744,10 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
             k_scan_big<<<B, kBlock, 0, st>>>(p);
             g_launches += 1;
             note(cudaGetLastError());
-            note(launch_k(h, k_mid<true>, dim3(gx + 1, B), kBlock, 0, st, p, 0, n2e));
+            note(launch_k(h, k_mid<true>, dim3(gx + 1, B), kBlock, 16 + (size_t)kWarps * kChunk * 2, st, p, 0, n2e));
         } else {
             const int sc = (std::max(chunks, 1) + 3) & ~3;
-            note(launch_k(h, k_mid<false>, dim3(gx + 1, B), kBlock, ((size_t)sc * 10 + 8 + 15) & ~(size_t)15, st, p, sc, n2e));
+            note(launch_k(h, k_mid<false>, dim3(gx + 1, B), kBlock, (((size_t)sc * 10 + 8 + 15) & ~(size_t)15) + (size_t)kWarps * kChunk * 2, st, p, sc, n2e));
         }
     }
     if (chunks > 0 && T > kChainMaxT) {
@@ -1431,6 +1433,24 @@ extern "C" int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes, uint6
     return BVX_OK;
 }
 
+extern "C" int bvx_frame_stats(bvx_handle* h, int32_t b, int32_t* cells, int32_t* voxels, int32_t* cutoff,
+                               int32_t* processed, void* stream)
+{
+    if (!h) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null handle");
+    if (b < 1 || b > h->cfg.max_frames) return fail(h, BVX_ERR_BAD_ARGUMENT, "b must be in [1, max_frames]");
+    CK(h, cudaSetDevice(h->device));
+    std::vector<FrameState> st((size_t)b);
+    CK(h, cudaMemcpyAsync(st.data(), h->d_state, sizeof(FrameState) * (size_t)b, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CK(h, cudaStreamSynchronize((cudaStream_t)stream));
+    for (int i = 0; i < b; ++i) {
+        if (cells) cells[i] = st[i].total;
+        if (voxels) voxels[i] = st[i].m;
+        if (cutoff) cutoff[i] = st[i].istar;
+        if (processed) processed[i] = st[i].n_done;
+    }
+    return BVX_OK;
+}
+
 // ------------------------------------------------------------------ profiling
 extern "C" int bvx_profile_enable(bvx_handle* h, int32_t on)
 {
@@ -1500,6 +1520,13 @@ extern "C" int bvx_scatter_bev_dev(const float* feats, const int32_t* coors4, co
     return scatter_bev(feats, coors4, m_cap, m_dev, c, b, d, ny, nx, canvas, stream);
 }
 
+// Voxel-index map of the BEV scatter, one per (device, stream) -- calls on one stream are ordered, calls on
+// different streams must not share it --, grown on demand and kept: its contents never need clearing
+// (see k_bev_canvas), so a call costs no fill.
+struct ScatterMap { int dev; cudaStream_t st; int* p; size_t count; };
+static std::mutex g_map_mu;
+static std::vector<ScatterMap> g_maps;
+
 static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, const int32_t* m_dev, int32_t c,
                        int32_t b, int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream)
 {
@@ -1509,17 +1536,49 @@ static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, con
     if (((uintptr_t)canvas & 15) || ((uintptr_t)coors4 & 15))
         return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "canvas/coors must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t total = (size_t)b * c * d * ny * nx;
-    const size_t n4 = total >> 2;
-    const int ntail = (int)(total & 3);
-    const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
-    k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(canvas), n4, canvas + (n4 << 2), ntail);
-    g_launches += 1;
-    if (m > 0) {
-        const long long work = (long long)m * c;
-        k_scatter<<<(unsigned)((work + kBlock - 1) / kBlock), kBlock, 0, st>>>(
-            feats, reinterpret_cast<const int4*>(coors4), m, c, b, d, ny, nx, canvas, m_dev);
+    const size_t cells = (size_t)b * d * ny * nx;
+    if (m == 0) {
+        // nothing to place: the canvas is all zeros
+        const size_t total = cells * c, n4 = total >> 2;
+        const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
+        k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(canvas), n4, canvas + (n4 << 2), (int)(total & 3));
         g_launches += 1;
+    } else {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        int* map = nullptr;
+        {
+            std::lock_guard<std::mutex> lk(g_map_mu);
+            ScatterMap* sm = nullptr;
+            for (ScatterMap& e : g_maps)
+                if (e.dev == dev && e.st == st) sm = &e;
+            if (!sm) {
+                g_maps.push_back(ScatterMap{dev, st, nullptr, 0});
+                sm = &g_maps.back();
+            }
+            if (sm->count < cells + 4) {
+                if (sm->p) { cudaStreamSynchronize(st); cudaFree(sm->p); sm->p = nullptr; sm->count = 0; }
+                cudaError_t e = cudaMalloc((void**)&sm->p, (cells + 4) * sizeof(int));
+                if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "scatter map: %s", cudaGetErrorString(e));
+                sm->count = cells + 4;
+            }
+            map = sm->p;
+        }
+        k_bev_map<<<(m + kBlock - 1) / kBlock, kBlock, 0, st>>>(reinterpret_cast<const int4*>(coors4), m, m_dev, b, d, ny, nx, map);
+        // channel slices: enough blocks to fill the GPU, at most 8 channels per thread
+        const bool vec = (nx & 3) == 0;
+        const long long groups = (long long)(cells / (vec ? 4 : 1));
+        const int gb = (int)((groups + kBlock - 1) / kBlock);
+        int ch_per = c;
+        while (ch_per > 8 || (ch_per > 1 && (long long)gb * ((c + ch_per - 1) / ch_per) < 148 * 8)) ch_per = (ch_per + 1) / 2;
+        const dim3 grid(gb, (c + ch_per - 1) / ch_per);
+        if (vec)
+            k_bev_canvas<4><<<grid, kBlock, 0, st>>>(feats, reinterpret_cast<const int4*>(coors4), m, m_dev, c, b, d, ny, nx,
+                                                     map, canvas, ch_per);
+        else
+            k_bev_canvas<1><<<grid, kBlock, 0, st>>>(feats, reinterpret_cast<const int4*>(coors4), m, m_dev, c, b, d, ny, nx,
+                                                     map, canvas, ch_per);
+        g_launches += 2;
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "scatter launch: %s", cudaGetErrorString(e));

@@ -43,6 +43,12 @@ constexpr int kInlineFrames = 64;      // calls of up to this many frames carry 
 #ifndef BVX_ABL
 #define BVX_ABL 0   // timing ablations of experiment builds (tools/variants.sh); 0 in the product
 #endif
+#ifndef BVX_GATHER_PF
+#define BVX_GATHER_PF 0
+#endif
+#ifndef BVX_GATHER_BLOCKS
+#define BVX_GATHER_BLOCKS 8
+#endif
 #ifndef BVX_INSERT_BLOCKS
 #define BVX_INSERT_BLOCKS 6   // 42 registers, no spills: 59.6 us against 76.4 us with 8 blocks of 32 registers (cfg4 break)
 #endif
@@ -51,6 +57,7 @@ struct GridParams {
     float lo[3];
     float vs[3];
     float rvs[3];  // 1 / vs rounded to nearest (NaN: always take the exact divide)
+    float mg[3];   // 2^-21 (grid + 1), rounded up: margin of the divide-free cell index
     float gsf[3];  // grid size as float, x y z
     int gs[3];     // x y z
 };
@@ -107,9 +114,9 @@ struct Pipe {
     unsigned long long* table;
     unsigned int* cand;
     unsigned int* lost;  // per point bit: was the cell's first point for a while, then displaced by an earlier one
-    unsigned char* unit8;     // per 128-point unit: number of candidate bits (0 .. 128)
+    unsigned char* unit8;     // per chunk 16 bytes: bytes 0-7 = candidate bits of its eight 128-point units (0 .. 128 each),
+                              // bytes 8-15 = displaced candidates per unit (two words, atomics; between calls: 0)
     unsigned int* chunkstat;  // per chunk: first occurrences (low 16 bits) | displaced candidates (high 16)
-    unsigned int* lunit32;    // per chunk two words = eight bytes: displaced candidates per unit (between calls: 0)
     int2* extras;        // per chunk, 1024 entries: {point index, table slot of its cell} of every in-range point
                          // that is not the first of its cell (as seen when it was inserted, or displaced later)
     int* extn;           // per chunk: entries on its extras list
@@ -186,27 +193,27 @@ __device__ __forceinline__ void xform(const SegDesc& sg, float& x, float& y, flo
 
 // floor(RN((v - lo) / size)), the reference's fp32 expression, without the divide where its result
 // is certain.  a = RN(v - lo); t = RN(a * RN(1/size)) differs from the correctly rounded quotient q
-// by less than 2^-22 |t| (three roundings of 2^-24 each), so whenever t lies further than
-// m = 2^-21 |t| from both neighbouring integers, floor(q) == floor(t).  Otherwise (about one point in a
-// thousand; also NaN, Inf, zero, |t| >= 2^21, a size whose reciprocal is not a normal number) the IEEE
-// divide decides.
-__device__ __forceinline__ float cell_axis(float v, float lo, float vs, float rvs)
-{
-    const float a = __fsub_rn(v, lo);
-    const float t = __fmul_rn(a, rvs);
-    float k = floorf(t);
-    const float fr = __fsub_rn(t, k);                                  // exact
-    const float m = __fmul_rn(fabsf(t), 4.76837158203125e-07f);        // 2^-21 |t|
-    if (!(fminf(fr, __fsub_rn(1.0f, fr)) > m)) k = floorf(__fdiv_rn(a, vs));
-    return k;
-}
-
+// by less than 2^-22 |t| (three roundings of 2^-24 each), so whenever t lies further than 2^-21 |t| from
+// both neighbouring integers, floor(q) == floor(t).  The margin is the constant mg = 2^-21 (grid + 1):
+// it covers every t in [-1, grid + 1], and outside that interval any floor on the right side of the grid
+// boundary classifies the point as out of range, which is all that is needed there.  Otherwise (about one
+// point in a thousand; also NaN, Inf, |t| >= 2^23, a size whose reciprocal is not a normal number: rvs = NaN)
+// the IEEE divide decides: ONE branch per point.
 // -1 if outside / NaN, else the linear cell index in the reference's zyx grid order.
 __device__ __forceinline__ int cell_of(const GridParams& g, float x, float y, float z)
 {
-    const float cx = cell_axis(x, g.lo[0], g.vs[0], g.rvs[0]);
-    const float cy = cell_axis(y, g.lo[1], g.vs[1], g.rvs[1]);
-    const float cz = cell_axis(z, g.lo[2], g.vs[2], g.rvs[2]);
+    const float ax = __fsub_rn(x, g.lo[0]), ay = __fsub_rn(y, g.lo[1]), az = __fsub_rn(z, g.lo[2]);
+    const float tx = __fmul_rn(ax, g.rvs[0]), ty = __fmul_rn(ay, g.rvs[1]), tz = __fmul_rn(az, g.rvs[2]);
+    float cx = floorf(tx), cy = floorf(ty), cz = floorf(tz);
+    const float fx = __fsub_rn(tx, cx), fy = __fsub_rn(ty, cy), fz = __fsub_rn(tz, cz);     // exact
+    // (a NaN makes its comparison false)
+    const bool safe = (fx > g.mg[0]) & (__fsub_rn(1.0f, fx) > g.mg[0]) & (fy > g.mg[1]) & (__fsub_rn(1.0f, fy) > g.mg[1]) &
+                      (fz > g.mg[2]) & (__fsub_rn(1.0f, fz) > g.mg[2]);
+    if (!safe) {
+        cx = floorf(__fdiv_rn(ax, g.vs[0]));
+        cy = floorf(__fdiv_rn(ay, g.vs[1]));
+        cz = floorf(__fdiv_rn(az, g.vs[2]));
+    }
     const bool ok = (cx >= 0.0f) && (cx < g.gsf[0]) && (cy >= 0.0f) && (cy < g.gsf[1]) &&
                     (cz >= 0.0f) && (cz < g.gsf[2]);
     if (!ok) return -1;
@@ -460,41 +467,62 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
         }
     }
     int2* ext = p.extras + (size_t)(fr.chunk_off + (base >> 10)) * kChunk;
-    while (__any_sync(0xffffffffu, active)) {          // warp-uniform rounds
+    // A displaced point o (it was its cell's first point until point i arrived) becomes an extra of the
+    // cell; its chunk counts one first point less and one displaced candidate more.
+    auto displaced = [&](unsigned int o, unsigned int slot) {
+        atomicOr(p.lost + fr.word_off + (o >> 5), 1u << (o & 31));
+        atomicAdd(p.chunkstat + fr.chunk_off + (o >> 10), 0xFFFFu);
+        atomicAdd(reinterpret_cast<unsigned int*>(p.unit8) + (size_t)(fr.chunk_off + (o >> 10)) * 4 + 2 + ((o >> 9) & 1u),
+                  1u << (((o >> 7) & 3u) * 8));
+        ext[atomicAdd(&s_extn[q], 1)] = make_int2((int)o, (int)slot);
+    };
+    {
+        // first round: one CAS per in-range point, all four in flight
         unsigned long long r[kPts];
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
-            const unsigned long long mine = ((unsigned long long)(unsigned)cell[k] << 32) |
-                                            (unsigned)(base + toff + k * 32);
             r[k] = 0;
             if (active & (1u << k))
-                r[k] = (needmin & (1u << k)) ? atomicMin(tbl + h[k], mine)
-                                             : atomicCAS(tbl + h[k], kEmpty64, mine);
+                r[k] = atomicCAS(tbl + h[k], kEmpty64,
+                                 ((unsigned long long)(unsigned)cell[k] << 32) | (unsigned)(base + toff + k * 32));
         }
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             const unsigned int bit = 1u << k;
             if (!(active & bit)) continue;
-            const unsigned int i = (unsigned)(base + toff + k * 32);
-            // a point that is done keeps, in h[k], the table slot of its cell
-            if (needmin & bit) {
-                const unsigned int o = (unsigned)r[k];
-                if (o > i) {
-                    // I am the cell's first point now; o no longer is: it becomes an extra of the
-                    // cell, its chunk counts one first point less and one displaced candidate more
-                    wonmask |= bit;
-                    atomicOr(p.lost + fr.word_off + (o >> 5), 1u << (o & 31));
-                    atomicAdd(p.chunkstat + fr.chunk_off + (o >> 10), 0xFFFFu);
-                    atomicAdd(p.lunit32 + (size_t)(fr.chunk_off + (o >> 10)) * 2 + ((o >> 9) & 1u), 1u << (((o >> 7) & 3u) * 8));
-                    ext[atomicAdd(&s_extn[q], 1)] = make_int2((int)o, (int)h[k]);
-                }
-                active &= ~bit;
-            } else if (r[k] == kEmpty64) {
+            if (r[k] == kEmpty64) {
                 wonmask |= bit; ++nnew; active &= ~bit;
             } else if ((unsigned)(r[k] >> 32) == (unsigned)cell[k]) {
-                if ((unsigned)r[k] > i) needmin |= bit; else active &= ~bit;
+                if ((unsigned)r[k] > (unsigned)(base + toff + k * 32)) needmin |= bit; else active &= ~bit;
             } else {
                 h[k] = (h[k] + 1) & fr.tbl_mask;
+            }
+        }
+    }
+    // Stragglers (a slot held by another cell: probe on; the cell's entry is a later point: atomicMin): a
+    // couple of lanes per warp, so each lane works on ONE of its points per round -- the rounds cost a quarter
+    // of a four-point round, and an atomic instruction with two active lanes costs as much as a full one.
+    while (__any_sync(0xffffffffu, active)) {
+        const int k = __ffs(active) - 1;                   // this lane's point of the round (-1: none left)
+        const unsigned int bit = active & (0u - active);
+        const unsigned int hk = k == 0 ? h[0] : (k == 1 ? h[1] : (k == 2 ? h[2] : h[3]));
+        const unsigned int ck = (unsigned)(k == 0 ? cell[0] : (k == 1 ? cell[1] : (k == 2 ? cell[2] : cell[3])));
+        const unsigned int i = (unsigned)(base + toff + k * 32);
+        const unsigned long long mine = ((unsigned long long)ck << 32) | i;
+        unsigned long long rr = 0;
+        if (bit) rr = (needmin & bit) ? atomicMin(tbl + hk, mine) : atomicCAS(tbl + hk, kEmpty64, mine);
+        if (bit) {
+            if (needmin & bit) {
+                const unsigned int o = (unsigned)rr;
+                if (o > i) { wonmask |= bit; displaced(o, hk); }
+                active &= ~bit;
+            } else if (rr == kEmpty64) {
+                wonmask |= bit; ++nnew; active &= ~bit;
+            } else if ((unsigned)(rr >> 32) == ck) {
+                if ((unsigned)rr > i) needmin |= bit; else active &= ~bit;
+            } else {
+                const unsigned int hn = (hk + 1) & fr.tbl_mask;
+                if (k == 0) h[0] = hn; else if (k == 1) h[1] = hn; else if (k == 2) h[2] = hn; else h[3] = hn;
             }
         }
     }
@@ -530,7 +558,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
                 for (int k = 0; k < kPts; ++k)
                     if (w0 + k < fr.nwords) p.cand[fr.word_off + w0 + k] = cw[k];
             }
-            p.unit8[(size_t)cidx * kWarps + wid] = (unsigned char)ncand;
+            p.unit8[(size_t)cidx * 16 + wid] = (unsigned char)ncand;
             if (ncand) atomicAdd(p.chunkstat + cidx, (unsigned)ncand);
         }
         if (next) {
@@ -687,7 +715,7 @@ __device__ __forceinline__ int rank_of(const Pipe& p, const FrameDesc& fr, unsig
                                        const unsigned short* s_lost)
 {
     const int c = (int)(fi >> 10), u = (int)(fi >> 7) & 7, wq = (int)(fi >> 5) & 3, b = (int)fi & 31;
-    const uint2 u8 = __ldg(reinterpret_cast<const uint2*>(p.unit8 + (size_t)(fr.chunk_off + c) * kWarps));
+    const uint4 u8 = __ldcg(reinterpret_cast<const uint4*>(p.unit8 + (size_t)(fr.chunk_off + c) * 16));
     const uint4 cw = __ldg(reinterpret_cast<const uint4*>(p.cand + fr.word_off + c * kChunkWords + u * kPts));
     int r, nlost;
     if (BIG) {
@@ -707,9 +735,8 @@ __device__ __forceinline__ int rank_of(const Pipe& p, const FrameDesc& fr, unsig
     r += __popc(cw.x & m0) + __popc(cw.y & m1) + __popc(cw.z & m2) + __popc(cw.w & m3);
     unsigned int mine = wq == 0 ? cw.x : (wq == 1 ? cw.y : (wq == 2 ? cw.z : cw.w));
     if (nlost) {
-        const uint2 l8 = __ldcg(reinterpret_cast<const uint2*>(p.lunit32 + (size_t)(fr.chunk_off + c) * 2));
         const uint4 lw = __ldcg(reinterpret_cast<const uint4*>(p.lost + fr.word_off + c * kChunkWords + u * kPts));
-        r -= (int)__vsadu4(l8.x & mlo, 0u) + (int)__vsadu4(l8.y & mhi, 0u);
+        r -= (int)__vsadu4(u8.z & mlo, 0u) + (int)__vsadu4(u8.w & mhi, 0u);
         r -= __popc(lw.x & m0) + __popc(lw.y & m1) + __popc(lw.z & m2) + __popc(lw.w & m3);
         mine &= ~(wq == 0 ? lw.x : (wq == 1 ? lw.y : (wq == 2 ? lw.z : lw.w)));
     }
@@ -763,6 +790,19 @@ __device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, in
     int r1 = v1 ? extra_rank<BIG>(p, fr, e1, s_pre, s_lost) : 0x7FFFFFFF;
     const bool chain = p.T <= kChainMaxT;
     int o0 = 0, o1 = 0;
+#if BVX_ABL == 5
+    if (r0 + r1 == -12345) p.vfirst[0] = 1;
+    return;
+#endif
+#if BVX_ABL == 6
+    if (chain) {
+        const int T1 = p.T - 1;
+        if ((unsigned)r0 < (unsigned)p.cap) o0 = p.bucket[((size_t)f * p.cap + r0) * T1];
+        if ((unsigned)r1 < (unsigned)p.cap) o1 = p.bucket[((size_t)f * p.cap + r1) * T1];
+        if (o0 + o1 == -12345) p.vfirst[0] = 1;
+        return;
+    }
+#endif
     if (chain) {
         const int T1 = p.T - 1;
         if ((unsigned)r0 < (unsigned)p.cap) o0 = atomicMin(p.bucket + ((size_t)f * p.cap + r0) * T1, e0.x);
@@ -772,7 +812,7 @@ __device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, in
     if ((unsigned)r1 < (unsigned)p.cap) place_extra(p, f, r1, e1.x, o1, chain);
 }
 
-// grid (gx + 1, B); dynamic smem (not BIG): (max chunks per frame + 1) x 10 bytes.  Every block of
+// grid (gx + 1, B); dynamic smem: (max chunks per frame + 1) x 10 bytes (not BIG) + 16 KB.  Every block of
 // frame f scans the frame's chunk counts in shared memory (<= 4096 ints: cheaper than a kernel boundary
 // and a last-block chain).  Then the blocks of a frame split by role, so that the three latency chains
 // run side by side instead of one after the other:
@@ -796,6 +836,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
     int* s_pre = s_dyn;                                  // [smem_chunks] exclusive prefix of the first-point counts
     int* s_epre = s_dyn + smem_chunks;                   // [smem_chunks + 1] exclusive prefix of the extras counts
     unsigned short* s_lost = reinterpret_cast<unsigned short*>(s_dyn + 2 * smem_chunks + 1);
+    unsigned short* s_stage = s_lost + ((smem_chunks + 1) & ~1);   // [kWarps][kChunk] first points of a chunk, per warp
     const int cap = p.cap;
     const bool brk = !p.overflow_continue;
     const int gx = gridDim.x - 1;
@@ -893,16 +934,24 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
                         if (nlost) fw &= ~__ldcg(p.lost + fr.word_off + w);
                     }
                 }
+                // the chunk's first points, compacted through shared memory (local index, 16 bits), so that
+                // vfirst is written with coalesced stores: one scattered 4-byte store per voxel cost a
+                // sector transaction each (1.3 M per step: 4.5 us of L1/L2 transaction time)
                 int tot;
-                int v = pre + warp_exclusive_scan(__popc(fw), lane, &tot);
-                int* vf = p.vfirst + (size_t)f * cap;
-                while (fw && v <= cap) {
-                    const int i = w * 32 + (__ffs(fw) - 1);
-                    if (v < cap) vf[v] = i;
-                    else if (brk && !BIG) st->istar = i;       // the point that would open voxel #cap
+                int k = warp_exclusive_scan(__popc(fw), lane, &tot);
+                unsigned short* stage = s_stage + wid * kChunk;
+                while (fw) {
+                    stage[k++] = (unsigned short)(lane * 32 + (__ffs(fw) - 1));
                     fw &= fw - 1;
-                    ++v;
                 }
+                __syncwarp();
+                int* vf = p.vfirst + (size_t)f * cap;
+                for (int j = lane; j < tot; j += 32) {
+                    const int v = pre + j, i = c * kChunk + stage[j];
+                    if (v < cap) vf[v] = i;
+                    else if (v == cap && brk && !BIG) st->istar = i;     // the point that would open voxel #cap
+                }
+                __syncwarp();
             }
             if (BIG && p.T > 1) {
                 // (frames of > 4 M points) the chunk's own extras, by the same warp
@@ -995,7 +1044,7 @@ __device__ __forceinline__ void tidy_frame(const Pipe& p, const FrameDesc& fr, i
     for (int w = blockIdx.x * kBlock + threadIdx.x; w < nwords; w += stride) p.lost[fr.word_off + w] = 0u;
     for (int c = blockIdx.x * kBlock + threadIdx.x; c < nch; c += stride) {
         p.chunkstat[fr.chunk_off + c] = 0u;
-        reinterpret_cast<uint2*>(p.lunit32)[fr.chunk_off + c] = make_uint2(0u, 0u);
+        reinterpret_cast<uint2*>(p.unit8)[(size_t)(fr.chunk_off + c) * 2 + 1] = make_uint2(0u, 0u);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         st->ticket = 0ull;
@@ -1019,13 +1068,36 @@ __device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int 
     }
 }
 
+// 16-byte asynchronous copy global -> shared (LDGSTS); src_bytes == 0 writes 16 zero bytes
+// without reading global memory: the zero padding of the voxel rows.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes)
+{
+    const unsigned int d = (unsigned int)__cvta_generic_to_shared(smem_dst);
+#if BVX_GATHER_PF == 128
+    asm volatile("cp.async.ca.shared.global.L2::128B [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+#elif BVX_GATHER_PF == 256
+    asm volatile("cp.async.ca.shared.global.L2::256B [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+#elif BVX_GATHER_PF == 64
+    asm volatile("cp.async.ca.shared.global.L2::64B [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+#else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+#endif
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
 // Fast path: T <= 8 (extras already sorted by the atomicMin chain), 4 floats per
-// point, 16-byte aligned rows.  One thread per voxel: T independent row loads in
-// flight, mean and coordinates from registers; the voxel rows go through a
-// per-warp shared-memory transpose so the [M, T, 4] store is fully coalesced.
+// point, 16-byte aligned rows.  One thread per voxel.  The T rows of a voxel are random 16-byte
+// reads: they are copied global -> shared ASYNCHRONOUSLY (cp.async, zero fill for the empty slots),
+// straight to their place in the warp's [32 voxels, T, 4] tile, so no registers are held while they
+// are in flight (24 registers, 8 blocks per SM: what bounds this kernel is the number of such reads
+// in flight); the tile then goes out with fully coalesced 16-byte streaming stores, and the thread
+// reads its own rows back for the coordinates and the fused mean.
 // grid (tiles + reset chunks, B); dynamic smem = kWarps * 32 * T * 16 bytes.
 template <int T>
-__global__ void __launch_bounds__(kBlock) k_gather_small(const __grid_constant__ Pipe p, int tiles)
+__global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(const __grid_constant__ Pipe p, int tiles)
 {
     extern __shared__ float4 smem_v[];
     pdl_prologue();
@@ -1064,26 +1136,20 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const __grid_constant__
         }
     }
     const float4* rows = reinterpret_cast<const float4*>(plain_rows(p, fr));
-    float4 row[T];
+    // voxel-major float4 index lane*T + s inside the warp's tile (even T: xor swizzle against bank conflicts)
+    float4* sw = smem_v + wid * (32 * T);
     int nvalid = 0;
 #pragma unroll
     for (int s = 0; s < T; ++s) {
-        row[s] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (idx[s] != kEmptyIdx) {
-            row[s] = __ldg(rows + idx[s]);
-            ++nvalid;
-        }
+        int q = lane * T + s;
+        if ((T & 1) == 0) q ^= (q >> 3) & 7;
+        const bool on = idx[s] != kEmptyIdx;
+        cp_async16(sw + q, rows + (on ? idx[s] : 0), on ? 16 : 0);
+        nvalid += on;
     }
+    cp_async_wait_all();
+    __syncwarp();
     if (p.voxels) {
-        // per-warp transpose: voxel-major float4 index lane*T + s, read back linearly
-        float4* sw = smem_v + wid * (32 * T);
-#pragma unroll
-        for (int s = 0; s < T; ++s) {
-            int q = lane * T + s;
-            if ((T & 1) == 0) q ^= (q >> 3) & 7;
-            sw[q] = row[s];
-        }
-        __syncwarp();
         const int wv0 = v0 + wid * 32;                    // first voxel of this warp
         const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
         float4* out = reinterpret_cast<float4*>(p.voxels) + (gbase + wv0) * T;
@@ -1095,6 +1161,11 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const __grid_constant__
             if (j < wn * T) __stcs(out + j, sw[q]);
         }
     }
+    auto own = [&](int slot) {                            // this voxel's rows, back from the tile
+        int q = lane * T + slot;
+        if ((T & 1) == 0) q ^= (q >> 3) & 7;
+        return sw[q];
+    };
     if (p.crow) {
         // compact rows for the host form: the tile reserves a range for its kept points, each voxel
         // writes its rows (slots 0 .. nvalid-1) at its prefix inside the range
@@ -1111,7 +1182,7 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const __grid_constant__
         float4* dst = p.crow + s_base + ex;
 #pragma unroll
         for (int s = 0; s < T; ++s)
-            if (s < nvalid) __stcs(dst + s, row[s]);
+            if (s < nvalid) __stcs(dst + s, own(s));
     }
     if (!live) return;
     const size_t gv = gbase + v;
@@ -1120,13 +1191,16 @@ __global__ void __launch_bounds__(kBlock) k_gather_small(const __grid_constant__
         for (int s = 0; s < T; ++s) p.idx_out[gv * T + s] = idx[s] == kEmptyIdx ? -1 : idx[s];
     }
     p.num_points[gv] = nvalid;
-    write_coor(p, f, gv, cell_of(p.g, row[0].x, row[0].y, row[0].z));
+    const float4 r0 = own(0);
+    write_coor(p, f, gv, cell_of(p.g, r0.x, r0.y, r0.z));
     if (p.mean_out) {
-        float sx = 0.f, sy = 0.f, sz = 0.f, swt = 0.f;
+        // sum over the T slots in slot order (zeros included), like the reference's features.sum(dim=1)
+        float sx = __fadd_rn(0.f, r0.x), sy = __fadd_rn(0.f, r0.y), sz = __fadd_rn(0.f, r0.z), swt = __fadd_rn(0.f, r0.w);
 #pragma unroll
-        for (int s = 0; s < T; ++s) {
-            sx = __fadd_rn(sx, row[s].x); sy = __fadd_rn(sy, row[s].y);
-            sz = __fadd_rn(sz, row[s].z); swt = __fadd_rn(swt, row[s].w);
+        for (int s = 1; s < T; ++s) {
+            const float4 r = own(s);
+            sx = __fadd_rn(sx, r.x); sy = __fadd_rn(sy, r.y);
+            sz = __fadd_rn(sz, r.z); swt = __fadd_rn(swt, r.w);
         }
         const float nf = (float)nvalid;
         const float m4[4] = {__fdiv_rn(sx, nf), __fdiv_rn(sy, nf), __fdiv_rn(sz, nf), __fdiv_rn(swt, nf)};
@@ -1303,24 +1377,73 @@ __global__ void __launch_bounds__(kBlock) k_fill_zero(float4* __restrict__ p, si
     if (blockIdx.x == 0 && (int)threadIdx.x < ntail) tail[threadIdx.x] = 0.f;
 }
 
-// one thread per (voxel, channel): canvas[b, c*D + z, y, x] = feats[i, c]
+// canvas[b, c*D + z, y, x] = feats[i, c] for coors4[i] = (b, z, y, x), zeros elsewhere
+// (torchplus.scatter_nd + the view of middle.py:522-525), as a GATHER: the canvas is channel-major, so a
+// voxel's C values lie H*W floats apart and scattering them costs one 4-byte transaction each, after a
+// separate zero fill.  Instead
+//   k_bev_map    : map[b, z, y, x] = i  (one 4-byte store per voxel; the map is NOT cleared first)
+//   k_bev_canvas : every thread owns 4 consecutive x of one (b, z, y) and writes them for a slice of the
+//                  channels as float4: each canvas byte is written exactly once, coalesced, zeros included.
+//                  A map entry v counts iff v < M and coors4[v] is this very cell -- that check is what makes
+//                  stale or uninitialised map contents harmless.
 // m_dev (optional): the number of voxels lives on the device (frame_voxel_offsets[B] of the call that
 // produced them); m is then the capacity the launch was sized for.
-__global__ void __launch_bounds__(kBlock) k_scatter(const float* __restrict__ feats,
-                                                    const int4* __restrict__ coors, int m, int c,
-                                                    int b, int d, int ny, int nx,
-                                                    float* __restrict__ canvas, const int* __restrict__ m_dev)
+__global__ void __launch_bounds__(kBlock) k_bev_map(const int4* __restrict__ coors, int m, const int* __restrict__ m_dev,
+                                                    int b, int d, int ny, int nx, int* __restrict__ map)
 {
-    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    const int i = blockIdx.x * kBlock + threadIdx.x;
     if (m_dev) m = min(m, __ldg(m_dev));
-    if (t >= (long long)m * c) return;
-    const int i = (int)(t / c), ch = (int)(t - (long long)i * c);
+    if (i >= m) return;
     const int4 q = __ldg(coors + i);
     if ((unsigned)q.x >= (unsigned)b || (unsigned)q.y >= (unsigned)d ||
         (unsigned)q.z >= (unsigned)ny || (unsigned)q.w >= (unsigned)nx)
         return;
-    const size_t o = ((((size_t)q.x * c + ch) * d + q.y) * ny + q.z) * nx + q.w;
-    canvas[o] = __ldg(feats + t);
+    map[(((size_t)q.x * d + q.y) * ny + q.z) * nx + q.w] = i;
+}
+
+// VEC = 4: nx % 4 == 0, float4 stores; VEC = 1: any nx.  grid (groups / 256, channel slices).
+template <int VEC>
+__global__ void __launch_bounds__(kBlock) k_bev_canvas(const float* __restrict__ feats, const int4* __restrict__ coors,
+                                                       int m, const int* __restrict__ m_dev, int c, int b, int d,
+                                                       int ny, int nx, const int* __restrict__ map,
+                                                       float* __restrict__ canvas, int ch_per)
+{
+    const int nxg = nx / VEC;
+    const long long g = (long long)blockIdx.x * kBlock + threadIdx.x;
+    if (g >= (long long)b * d * ny * nxg) return;
+    if (m_dev) m = min(m, __ldg(m_dev));
+    const int xg = (int)(g % nxg);
+    long long r = g / nxg;
+    const int y = (int)(r % ny); r /= ny;
+    const int z = (int)(r % d);
+    const int bb = (int)(r / d);
+    const size_t cell0 = (((size_t)bb * d + z) * ny + y) * nx + (size_t)xg * VEC;
+    int v[VEC];
+    if (VEC == 4) {
+        const int4 mv = __ldg(reinterpret_cast<const int4*>(map + cell0));
+        v[0] = mv.x; v[1 % VEC] = mv.y; v[2 % VEC] = mv.z; v[3 % VEC] = mv.w;
+    } else {
+        v[0] = __ldg(map + cell0);
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        bool ok = (unsigned)v[j] < (unsigned)m;
+        if (ok) {
+            const int4 q = __ldg(coors + v[j]);
+            ok = q.x == bb && q.y == z && q.z == y && q.w == xg * VEC + j;
+        }
+        if (!ok) v[j] = -1;
+    }
+    const int ch0 = blockIdx.y * ch_per, ch1 = min(c, ch0 + ch_per);
+    const size_t plane = (size_t)d * ny * nx;
+    float* out = canvas + ((size_t)bb * c + ch0) * plane + ((size_t)z * ny + y) * nx + (size_t)xg * VEC;
+    for (int ch = ch0; ch < ch1; ++ch, out += plane) {
+        float o[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) o[j] = v[j] >= 0 ? __ldg(feats + (size_t)v[j] * c + ch) : 0.0f;
+        if (VEC == 4) *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1 % VEC], o[2 % VEC], o[3 % VEC]);
+        else out[0] = o[0];
+    }
 }
 
 }  // namespace bvx

@@ -64,6 +64,7 @@ class VoxelGenerator:
             self._point_cloud_range.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), gs))
         self._grid_size = np.array(list(gs), dtype=np.int64)
         self._handle = None
+        self._captured = []          # (graph, private generator) pairs made by capture()
         self._cap = dict(max_points=0, max_frames=0, max_voxels=0, max_point_features=0)
 
     # ---- attributes the reference reads (second_builder.py:17-18, train.py:135)
@@ -166,6 +167,18 @@ class VoxelGenerator:
                    self._handle)
         return int(a.value), int(b.value), int(r.value)
 
+    def frame_stats(self, b):
+        """Per-frame facts of the last call (frames 0 .. b-1): dict of int32 arrays ``cells`` (distinct in-range
+        cells among the points looked at), ``voxels`` (M), ``cutoff`` (break mode: the point the reference's loop
+        stops at) and ``processed`` (points that went through the insert kernel: a prefix of the frame in break
+        mode).  Synchronises."""
+        if self._handle is None:
+            raise RuntimeError("frame_stats() needs a live handle: call generate once first")
+        arrs = [np.zeros(b, np.int32) for _ in range(4)]
+        ptrs = [a.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)) for a in arrs]
+        _lib.check(_lib.load().bvx_frame_stats(self._handle, b, *ptrs, None), self._handle)
+        return dict(zip(("cells", "voxels", "cutoff", "processed"), arrs))
+
     def profile(self, on=True):
         """Per-kernel device timing (CUDA events around every launch) on/off."""
         if self._handle is None:
@@ -229,14 +242,22 @@ class VoxelGenerator:
     def capture(self, points, max_voxels=None):
         """CUDA-graph the padded device form on a static ``points`` buffer: returns ``(graph, outputs)``
         with ``outputs = (voxels, coors, num_points, voxel_num[1])`` at capacity.  Copy a new frame of the
-        same size into ``points`` and ``graph.replay()``: the four kernels (with their programmatic
-        dependent-launch edges) run without any Python or launch overhead (cfg1: 43 us instead of 75)."""
+        same size into ``points`` and ``graph.replay()``: the three kernels (with their programmatic
+        dependent-launch edges) run without any Python or launch overhead.
+
+        The graph gets a generator (handle, workspace, descriptors) of its own, kept alive by this one:
+        later calls on this generator -- other frame sizes, handle growth -- cannot disturb a replay."""
         import torch
-        self.generate_padded(points, max_voxels)         # outside capture: uploads the frame layout
+        own = VoxelGenerator(self._voxel_size, self._point_cloud_range, self._max_num_points, self._max_voxels,
+                             overflow=self._overflow, grid=self._grid, device=self._device,
+                             prefix_upload=self._prefix_upload, host_assemble=self._host_assemble,
+                             host_threads=self._host_threads)
+        own.generate_padded(points, max_voxels)          # outside capture: allocates the handle, warms the kernels
         torch.cuda.synchronize(points.device)
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
-            out = self.generate_padded(points, max_voxels)
+            out = own.generate_padded(points, max_voxels)
+        self._captured.append((graph, own))
         return graph, out
 
     def generate_padded(self, points, max_voxels=None):
@@ -318,7 +339,8 @@ class VoxelGenerator:
             total += int(p.shape[0])
         return f_in, total
 
-    def generate_batched_sweeps(self, frames, max_voxels=None, append_dt=True, mean_channels=0, crops=None):
+    def generate_batched_sweeps(self, frames, max_voxels=None, append_dt=True, mean_channels=0, crops=None,
+                                padded=False, out=None):
         """B frames, each a list of sweeps ``(points[N_s, F_in], R or None, t or None, dt[, perm])``, key frame
         first: the batched form of ``generate_sweeps``.  ``append_dt=False`` keeps F_out = F_in; with
         one transformed sweep per frame that is the reference's global rotation / scaling / flip
@@ -328,7 +350,8 @@ class VoxelGenerator:
         (second/core/geometry.py:84-93); points with ``x*a + y*b + z*c + d >= 0`` for any surface are
         dropped before the transform, which is ``remove_outside_points`` (box_np_ops.py:645-657).
         Returns ``(voxels [sum M, T, F_out], coors [sum M, 4], num_points, frame_voxel_offsets
-        [B + 1][, mean])`` -- CUDA tensors for CUDA input, numpy arrays for numpy input."""
+        [B + 1][, mean])`` -- CUDA tensors for CUDA input, numpy arrays for numpy input.  ``padded=True`` (CUDA
+        input) skips the host sync and returns the capacity-sized buffers; ``out=`` reuses a previous such return."""
         import torch
         max_voxels = int(max_voxels or self._max_voxels)
         b = len(frames)
@@ -364,17 +387,27 @@ class VoxelGenerator:
         h = self._ensure(total, max(b, nsw), max_voxels, f_out, dev.index)
         tt, cap = self._max_num_points, b * max_voxels
         with torch.cuda.device(dev):
-            voxels = torch.empty((cap, tt, f_out), dtype=torch.float32, device=dev)
-            coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
-            num = torch.empty((cap,), dtype=torch.int32, device=dev)
-            fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
-            mean = (torch.empty((cap, mean_channels), dtype=torch.float32, device=dev)
-                    if mean_channels > 0 else None)
+            if out is not None:
+                voxels, coors, num, fvo = out[:4]
+                mean = out[4] if mean_channels > 0 else None
+                if (tuple(voxels.shape) != (cap, tt, f_out) or tuple(coors.shape) != (cap, 4) or num.shape[0] != cap
+                        or fvo.shape[0] != b + 1):
+                    raise ValueError("out= buffers do not match this call's capacity shapes")
+            else:
+                voxels = torch.empty((cap, tt, f_out), dtype=torch.float32, device=dev)
+                coors = torch.empty((cap, 4), dtype=torch.int32, device=dev)
+                num = torch.empty((cap,), dtype=torch.int32, device=dev)
+                fvo = torch.empty((b + 1,), dtype=torch.int32, device=dev)
+                mean = (torch.empty((cap, mean_channels), dtype=torch.float32, device=dev)
+                        if mean_channels > 0 else None)
             st = torch.cuda.current_stream(dev).cuda_stream
             _lib.check(_lib.load().bvx_generate_batched_sweeps(
                 h, arr, so.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), b, f_in, 1 if append_dt else 0,
                 carr, max_voxels, voxels.data_ptr(), coors.data_ptr(), num.data_ptr(), fvo.data_ptr(),
                 mean.data_ptr() if mean is not None else None, mean_channels, st), h)
+            if padded and use_torch:
+                self._keep = keep                     # the sweep tensors must outlive the enqueued kernels
+                return (voxels, coors, num, fvo) + ((mean,) if mean is not None else ())
             m = int(fvo[-1].item())
         out = (voxels[:m], coors[:m], num[:m], fvo) + ((mean[:m],) if mean is not None else ())
         if not use_torch:
@@ -523,20 +556,34 @@ class VoxelGenerator:
         return voxels[:m], coors[:m], num[:m], fvo
 
 
+class _PinnedBuffer:
+    """Owner of one bvx_host_alloc block; numpy arrays made from it keep it alive (``arr.base`` chain) and
+    the block goes back to the driver when the last of them is collected."""
+
+    def __init__(self, nbytes):
+        p = ctypes.c_void_p()
+        _lib.check(_lib.load().bvx_host_alloc(ctypes.byref(p), max(nbytes, 16)))
+        self.ptr = p
+        self.nbytes = max(nbytes, 16)
+        self.__array_interface__ = {"shape": (self.nbytes,), "typestr": "|u1", "data": (p.value, False), "version": 3}
+
+    def __del__(self):
+        try:
+            if self.ptr is not None:
+                _lib.load().bvx_host_free(self.ptr)
+                self.ptr = None
+        except Exception:
+            pass
+
+
 def pinned_empty(shape, dtype=np.float32):
-    """numpy array backed by pinned host memory (bvx_host_alloc); the host forms
-    DMA straight from/to it.  Keep the returned array alive while it is in use."""
+    """numpy array backed by pinned host memory (bvx_host_alloc); the host forms DMA straight from/to it.
+    The memory is released (bvx_host_free) when the array and every view of it are gone."""
     dtype = np.dtype(dtype)
-    nbytes = int(np.prod(shape)) * dtype.itemsize
-    p = ctypes.c_void_p()
-    _lib.check(_lib.load().bvx_host_alloc(ctypes.byref(p), max(nbytes, 16)))
-    buf = (ctypes.c_char * max(nbytes, 16)).from_address(p.value)
-    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
-    _PINNED[id(buf)] = (buf, p)
-    return arr
-
-
-_PINNED = {}
+    count = int(np.prod(shape))
+    owner = _PinnedBuffer(count * dtype.itemsize)
+    raw = np.asarray(owner)                               # uint8 view; raw.base is the owner
+    return raw[:count * dtype.itemsize].view(dtype).reshape(shape)
 
 
 def collate_points(frames, pinned=True):

@@ -1,18 +1,23 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the voxelization hot path.
 
-Metric (BASELINE.json): voxelized Mpoints/s (input points, counted before range
-filtering), with the fraction of the HBM roofline of the dominant kernel and the
-CPU oracle timed on this box's host cores.
+Metric (BASELINE.json): voxelized Mpoints/s (input points offered to the call, counted
+before range filtering and before the break cut-off), with the fraction of the HBM
+roofline of the dominant kernel and the CPU oracle timed on this box's host cores.
 
-Workload at every N: BASELINE cfg4 -- 64 synthetic KITTI-shaped 120k-point frames
-PER GPU (frames shard by index, weak scaling, no collective on the data path),
-SECOND car voxelizer 0.05 x 0.05 x 0.1 m, T=5, max_voxels=20000, overflow=break,
-mean VFE fused into the gather.  A "step" = one pass of generate_batched over the
-rank's 64 frames.
+    python bench.py --gpus N --steps K --warmup W                  (our arm, BASELINE cfg4)
+    python bench.py --impl reference ...                           (CPU oracle, all host threads)
+    python bench.py --config cfg1|cfg2|cfg3|cfg4|cfg5 [--overflow continue] [--scaling strong]
 
-    python bench.py --gpus N --steps K --warmup W          (our arm)
-    python bench.py --impl reference ...                   (CPU oracle, all host threads)
+Workloads (a "step" = one pass of the hot path over the rank's frames):
+  cfg4  (default, headline) 64 KITTI-shaped 120k-point frames PER GPU (weak scaling; frames shard by index,
+        no collective on the data path), SECOND car voxelizer, T=5, max_voxels=20000, mean VFE fused.
+        --scaling strong: 64 frames in TOTAL, 64/N per rank (the literal BASELINE cfg4).
+  cfg1  one such frame per step (generate);        cfg2  5-sweep nuScenes-shaped merge, T=10 (generate_sweeps);
+  cfg3  PointPillars: pillars -> mean VFE -> BEV canvas (fused generate_bev and the three-call path);
+  cfg5  Waymo-scale 3 x 180k points, 150k voxels, hashed grid.
+  Single-frame configs are timed (i) one call after the other, (ii) as a CUDA-graph replay where the entry
+  point allows it, (iii) as a 64-frame batch of the same shape (`--frames`).
 """
 import argparse
 import importlib
@@ -33,22 +38,51 @@ PKG = "3dobject_detection_temporal_b200"
 
 METRIC = "voxelized_points_per_second"
 UNIT = "Mpoints/s"
-WORKLOAD = ("cfg4: 64 KITTI-shaped 120k-point frames per GPU, SECOND car voxelizer "
-            "0.05x0.05x0.1 m, T=5, max_voxels=20000, overflow=break, hashed grid, fused mean VFE")
+WORKLOADS = {
+    "cfg1": "cfg1: one KITTI-shaped 120k-point frame per step, SECOND car voxelizer 0.05x0.05x0.1 m, T=5, max_voxels=20000",
+    "cfg2": "cfg2: temporal 5-sweep merge (+dt channel), nuScenes-shaped 34k points per sweep, 0.1x0.1x0.2 m, T=10, max_voxels=60000",
+    "cfg3": "cfg3: PointPillars 0.16 m pillars, T=100, max_voxels=12000, mean VFE + BEV scatter to a 432x496 canvas",
+    "cfg4": "cfg4: 64 KITTI-shaped 120k-point frames per GPU, SECOND car voxelizer 0.05x0.05x0.1 m, T=5, "
+            "max_voxels=20000, hashed grid, fused mean VFE",
+    "cfg5": "cfg5: Waymo-scale 3 sweeps x 180k points (+dt channel), 0.1x0.1x0.15 m, T=5, max_voxels=150000, hashed grid",
+}
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--frames", type=int, default=64, help="frames per GPU")
+    ap.add_argument("--config", default="cfg4", choices=sorted(WORKLOADS))
+    ap.add_argument("--frames", type=int, default=None, help="frames per GPU (default: 64 for cfg4, 1 otherwise)")
     ap.add_argument("--overflow", default="break", choices=["break", "continue"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the continue-mode, strong-scaling and 200-step legs")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not pin the process to the GPU's NUMA node")
     return ap.parse_args()
+
+
+def config_dict(args, world):
+    """`config` of the JSON line: the same keys and values in both arms."""
+    frames = frames_per_gpu(args, world)
+    big = args.config == "cfg4" and frames * 120000 * 16 * Arm.NSETS > 126e6
+    return {"workload": WORKLOADS[args.config], "config_id": args.config, "overflow": args.overflow,
+            "scaling": args.scaling, "frames_per_gpu": frames,
+            "l2": f"inputs rotate over {Arm.NSETS} distinct batches"
+                  + (" (together > 126 MB L2)" if big else
+                     " (they fit the 126 MB L2: a single frame is latency-bound, not bandwidth-bound)")
+                  + "; outputs rewritten every step; no explicit flush"}
+
+
+def frames_per_gpu(args, world):
+    if args.frames is not None:
+        return args.frames
+    if args.config == "cfg4":
+        return 64 // world if args.scaling == "strong" else 64
+    return 1
 
 
 def measured_peaks():
@@ -60,6 +94,18 @@ def measured_peaks():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(config, overflow, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full
+    capture of this workload (profiles/ncu_traffic.json, written by tools/ncu_summaries.py), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+        e = t[f"{config}/{overflow}"]
+        return float(e["kernels"][kernel]), e["source"]
+    except Exception:
+        return None, None
 
 
 class ClockSampler:
@@ -114,74 +160,113 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-# --------------------------------------------------------------------- workload
-def build_frames(synth, rank, world, frames_per_gpu):
-    """The rank's shard of the 64*world-frame job: global frame g -> rank g % world
-    (DistributedSampler interleave), seed = global frame index."""
+# --------------------------------------------------------------------- workloads
+def frame_seeds(args, rank, world):
+    """Global frame indices of this rank: frame g -> rank g % world (DistributedSampler interleave)."""
     pkg = importlib.import_module(PKG)
-    idx = pkg.shard_frames(frames_per_gpu * world, rank, world)
-    c = synth.CONFIGS["cfg4"]
-    return [synth.lidar_frame(c["n"], c["sensor"], c["seed0"] + g) for g in idx], c
+    per = frames_per_gpu(args, world)
+    return pkg.shard_frames(per * world, rank, world)
 
 
-def algorithmic_bytes(n_points, f, m_voxels, t, mean_c):
-    """SURVEY.md 8(d): generate = 4*(N*F_in + M*T*F_out + 4*M (batched coords) + M);
-    fused mean VFE adds its compulsory output 4*M*C."""
-    return dict(points_in=4 * n_points * f,
-                voxels_out=4 * m_voxels * t * f,
-                coors_out=16 * m_voxels,
-                num_out=4 * m_voxels,
-                mean_out=4 * m_voxels * mean_c)
+def build_host_frames(synth, cfg_name, seeds, variant=0):
+    """Per frame: list of sweeps (points, R, t, dt); single-sweep configs have one sweep with R = t = None.
+    `variant` shifts the seeds: distinct batches for the L2-hygiene rotation and the e2e rotation."""
+    c = synth.CONFIGS[cfg_name]
+    out = []
+    for g in seeds:
+        s0 = c["seed0"] + 1000 * variant + g * max(c["sweeps"], 1)
+        if c["sweeps"] == 1:
+            out.append([(synth.lidar_frame(c["n"], c["sensor"], s0), None, None, 0.0)])
+        else:
+            out.append(synth.lidar_sweeps(c["sweeps"], c["n"], c["sensor"], s0, c["dt"]))
+    return out, c
+
+
+def contract_bytes(cfg_name, n_points, f_in, f_out, m_voxels, t, mean_c, canvas_floats=0, fused=False):
+    """SURVEY.md 8(d) / BASELINE.md section 3: compulsory I/O at the contract boundary."""
+    if fused:      # points -> canvas entry point: 4*(N*F_in + B*C*ny*nx)
+        return dict(points_in=4 * n_points * f_in, canvas_out=4 * canvas_floats)
+    d = dict(points_in=4 * n_points * f_in, voxels_out=4 * m_voxels * t * f_out, coors_out=16 * m_voxels,
+             num_out=4 * m_voxels)
+    if mean_c:
+        d["mean_out"] = 4 * m_voxels * mean_c
+    return d
 
 
 # ------------------------------------------------------------------ CPU baseline
-def cpu_oracle_single_core(frames, c, overflow, budget_s=12.0):
+def oracle_generator(c, overflow):
+    import oracle
+    return oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
+                                       c["max_voxels"], overflow)
+
+
+def merged(frame):
+    """The oracle's input for one frame: the merged cloud (sweeps transformed, dt appended)."""
+    import oracle
+    if len(frame) == 1 and frame[0][1] is None:
+        return frame[0][0]
+    return oracle.merge_sweeps(frame)
+
+
+def cpu_frame_pass(g, c, pts, bufs, cfg_name):
+    """One frame through the C oracle kernel (+ the reference's mean VFE and scatter math for cfg3)."""
+    import oracle
+    v, co, nu = bufs
+    v.fill(0); nu.fill(0)                                            # the reference zero-allocates
+    m = g.kernel(pts, c["max_voxels"], v, co, nu)
+    if cfg_name == "cfg3":
+        feat = oracle.mean_vfe(v[:m], nu[:m])
+        gs = oracle.grid_size(c["voxel_size"], c["point_cloud_range"])
+        co4 = np.concatenate([np.zeros((m, 1), np.int32), co[:m]], axis=1)
+        oracle.scatter_bev(feat, co4, 1, int(gs[2]), int(gs[1]), int(gs[0]))
+    return m
+
+
+def cpu_oracle_single_core(frames, c, overflow, cfg_name, budget_s=12.0):
     """Variant A of BASELINE.md section 4: the C oracle (spconv C++ twin), 1 core, kernel
     only -- dense grid cached and reset, outputs pre-allocated."""
-    import oracle
-    g = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
-                                    c["max_voxels"], overflow)
-    t_, f = c["max_num_points"], frames[0].shape[1]
-    voxels = np.zeros((c["max_voxels"], t_, f), np.float32)
-    coors = np.zeros((c["max_voxels"], 3), np.int32)
-    num = np.zeros((c["max_voxels"],), np.int32)
-    g.kernel(frames[0], c["max_voxels"], voxels, coors, num)        # warm: page in the grid
-    done, t_kernel = 0, 0.0
+    g = oracle_generator(c, overflow)
+    clouds = [merged(fr) for fr in frames]
+    t_, f = c["max_num_points"], clouds[0].shape[1]
+    bufs = (np.zeros((c["max_voxels"], t_, f), np.float32), np.zeros((c["max_voxels"], 3), np.int32),
+            np.zeros((c["max_voxels"],), np.int32))
+    g.kernel(clouds[0], c["max_voxels"], *bufs)                       # warm: page in the grid
+    done, t_kernel, passes = 0, 0.0, 0
     t_start = time.perf_counter()
-    while time.perf_counter() - t_start < budget_s:
-        for fr in frames:
-            voxels.fill(0); num.fill(0)                              # the reference zero-allocates
+    while time.perf_counter() - t_start < budget_s and passes < 40:
+        for pts in clouds:
             t0 = time.perf_counter()
-            g.kernel(fr, c["max_voxels"], voxels, coors, num)
+            cpu_frame_pass(g, c, pts, bufs, cfg_name)
             t_kernel += time.perf_counter() - t0
-            done += fr.shape[0]
-        if done >= 40 * sum(fr.shape[0] for fr in frames):
-            break
+            done += pts.shape[0]
+            if time.perf_counter() - t_start > budget_s:
+                break
+        passes += 1
     return done / t_kernel / 1e6, done
 
 
-def cpu_oracle_all_threads(frames, c, overflow, steps, warmup):
+def cpu_oracle_all_threads(frames, c, overflow, steps, warmup, cfg_name):
     """The reference's own parallelisation model: P workers, one frame each
     (num_workers in second/pytorch/train.py:259-266).  P threads over the C oracle
     (ctypes releases the GIL), each with its own cached dense grid."""
     import concurrent.futures as cf
     import oracle
     import psutil
-    cores = os.cpu_count() or 1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     grid_bytes = int(np.prod(oracle.grid_size(c["voxel_size"], c["point_cloud_range"]))) * 4
     mem_ok = max(1, int(psutil.virtual_memory().available * 0.5 // (grid_bytes + (8 << 20))))
-    p = max(1, min(cores, len(frames), mem_ok))
-    gens = [oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
-                                        c["max_voxels"], overflow) for _ in range(p)]
-    t_, f = c["max_num_points"], frames[0].shape[1]
+    clouds = [merged(fr) for fr in frames]
+    p = max(1, min(cores, mem_ok))
+    if len(clouds) < p:                        # single-frame configs: every thread gets a frame of the same shape
+        clouds = [clouds[i % len(clouds)] for i in range(p)]
+    gens = [oracle_generator(c, overflow) for _ in range(p)]
+    t_, f = c["max_num_points"], clouds[0].shape[1]
     bufs = [(np.zeros((c["max_voxels"], t_, f), np.float32), np.zeros((c["max_voxels"], 3), np.int32),
              np.zeros((c["max_voxels"],), np.int32)) for _ in range(p)]
 
     def work(w):
-        g, (v, co, nu) = gens[w], bufs[w]
-        for k in range(w, len(frames), p):
-            v.fill(0); nu.fill(0)
-            g.kernel(frames[k], c["max_voxels"], v, co, nu)
+        for k in range(w, len(clouds), p):
+            cpu_frame_pass(gens[w], c, clouds[k], bufs[w], cfg_name)
 
     with cf.ThreadPoolExecutor(p) as ex:
         for _ in range(max(warmup, 1)):
@@ -190,27 +275,29 @@ def cpu_oracle_all_threads(frames, c, overflow, steps, warmup):
         for _ in range(steps):
             list(ex.map(work, range(p)))
         dt = time.perf_counter() - t0
-    return dt / steps, p
+    return dt / steps, p, sum(x.shape[0] for x in clouds), len(clouds)
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return 0
     pkg = importlib.import_module(PKG)
-    frames, c = build_frames(pkg.synth, 0, 1, args.frames)
-    npts = sum(f.shape[0] for f in frames)
+    frames, c = build_host_frames(pkg.synth, args.config, frame_seeds(args, 0, 1))
     steps = max(1, min(args.steps, 20))
-    sec, p = cpu_oracle_all_threads(frames, c, args.overflow, steps, min(args.warmup, 2))
+    warmup = max(args.warmup, 3)
+    sec, p, npts, nfr = cpu_oracle_all_threads(frames, c, args.overflow, steps, min(warmup, 3), args.config)
     val = npts / sec / 1e6
-    sample = f"{len(frames)} frames x {c['n']} points per step, {steps} steps, C oracle, one frame per thread"
+    sample = (f"{nfr} frames ({npts} points) per step, {steps} steps, C oracle"
+              + (" + mean VFE + BEV scatter" if args.config == "cfg3" else "") + ", one frame per thread")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": steps, "warmup": min(args.warmup, 2), "ms_per_step": sec * 1e3,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "steps": args.steps, "warmup": warmup, "ms_per_step": sec * 1e3,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "overflow": args.overflow,
-                       "note": "CPU restatement of the reference voxelizer (spconv is not in the reference "
-                               "tree); the reference arm does not scale with GPUs"},
+            "config": config_dict(args, world),
+            "note": "CPU restatement of the reference voxelizer (spconv is not in the reference tree); the "
+                    f"reference arm does not scale with GPUs; steps actually timed: {steps}",
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": p, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -219,11 +306,261 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------- ours
+class Arm:
+    """One workload on this rank: device inputs (NSETS rotating batches), a `step(i)` that enqueues one pass
+    of the hot path without synchronising, and the bookkeeping the JSON line needs."""
+    NSETS = 3
+
+    def __init__(self, args, pkg, torch, dev, rank, world, overflow=None, frames=None):
+        self.args, self.pkg, self.torch, self.dev = args, pkg, torch, dev
+        self.cfg = args.config
+        self.overflow = overflow or args.overflow
+        seeds = frame_seeds(args, rank, world)
+        if frames is not None:
+            seeds = pkg.shard_frames(frames * world, rank, world)
+        self.seeds = seeds
+        self.host_sets = []
+        for k in range(self.NSETS):
+            fr, c = build_host_frames(pkg.synth, self.cfg, seeds, variant=k)
+            self.host_sets.append(fr)
+        self.c = c
+        self.B = len(seeds)
+        self.T, self.cap = c["max_num_points"], c["max_voxels"]
+        self.sweeps = c["sweeps"] > 1
+        self.f_in = 4
+        self.f_out = 5 if self.sweeps else 4
+        self.npts = sum(s[0].shape[0] for fr in self.host_sets[0] for s in fr)
+        self.gen = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], self.T, self.cap,
+                                      overflow=self.overflow, device=dev)
+        self.mean_c = 4 if self.cfg in ("cfg4", "cfg1") else 0
+        self.dsets = []
+        for fr in self.host_sets:
+            if self.sweeps:
+                self.dsets.append([[(torch.from_numpy(p).to(dev), R, t, dt) for p, R, t, dt in f] for f in fr])
+            else:
+                cat = np.concatenate([f[0][0] for f in fr], axis=0)
+                self.dsets.append(torch.from_numpy(cat).to(dev))
+        self.offs = np.concatenate([[0], np.cumsum([f[0][0].shape[0] for f in self.host_sets[0]])]).astype(np.int32)
+        self.out = None
+        self.input_bytes = self.npts * 16
+
+    # -- device-form passes (no host sync inside)
+    def step(self, i):
+        g, d = self.gen, self.dsets[i % self.NSETS]
+        if self.cfg == "cfg3":
+            self.out = g.generate_bev(d, self.offs, channels=4, out=self.out)
+        elif self.sweeps:
+            self.out = g.generate_batched_sweeps(d, padded=True, out=self.out)
+        else:
+            self.out = g.generate_batched(d, self.offs, mean_channels=self.mean_c, padded=True, out=self.out)
+
+    def voxels(self):
+        self.torch.cuda.synchronize()
+        fvo = self.out[4] if self.cfg == "cfg3" else self.out[3]
+        return int(fvo[-1].item())
+
+    def bytes(self, m_voxels):
+        if self.cfg == "cfg3":
+            gx, gy, gz = (int(x) for x in self.gen.grid_size)
+            return contract_bytes(self.cfg, self.npts, 4, 4, m_voxels, self.T, 4,
+                                  canvas_floats=self.B * 4 * gz * gy * gx, fused=True)
+        return contract_bytes(self.cfg, self.npts, self.f_in, self.f_out, m_voxels, self.T, self.mean_c)
+
+    def time_steps(self, steps, warmup, dist=None, world=1):
+        torch = self.torch
+        for i in range(warmup):
+            self.step(i)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        l0 = self.pkg._lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            self.step(i)
+        e1.record()
+        torch.cuda.synchronize()
+        launches = self.pkg._lib.launch_count() - l0
+        ms_total = e0.elapsed_time(e1)
+        if world > 1:
+            dist.barrier()
+            t = torch.tensor([ms_total], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_total = float(t.item())
+        return ms_total / steps, launches
+
+    def per_kernel(self, steps):
+        self.gen.profile(True)
+        for i in range(steps):
+            self.step(i)
+        self.torch.cuda.synchronize()
+        prof = self.gen.profile_read()
+        self.gen.profile(False)
+        return {k: v[0] / max(v[1], 1) for k, v in prof.items()}
+
+    def close(self):
+        self.gen.close()
+
+
+def roofline_block(arm, ms_step, per_kernel, m_voxels, peak, peak_src):
+    """The dominant kernel's achieved bandwidth on ALGORITHMIC bytes (contract: every offered byte; touched: the
+    bytes the kernel really had to read -- in break mode k_insert stops handing out chunks behind the cut-off),
+    live CUDA-event kernel time, and the same for the whole pipeline."""
+    ab = arm.bytes(m_voxels)
+    st = arm.gen.frame_stats(arm.B)
+    processed = int(st["processed"].sum())
+    touched_in = 4 * arm.f_in * processed
+    k_bytes = {"k_insert": ab["points_in"],
+               "k_gather": sum(v for k, v in ab.items() if k != "points_in")}
+    k_touched = {"k_insert": touched_in, "k_gather": k_bytes["k_gather"]}
+    ksum = sum(per_kernel.values())
+    dom = max(per_kernel, key=per_kernel.get)
+    dom_bytes = k_bytes.get(dom, 0)
+    achieved = dom_bytes / (per_kernel[dom] * 1e-3) / 1e9
+    achieved_t = k_touched.get(dom, 0) / (per_kernel[dom] * 1e-3) / 1e9
+    pipe_bytes = sum(ab.values())
+    pipe_touched = pipe_bytes - ab["points_in"] + touched_in
+    pipe_gbs = pipe_bytes / (ms_step * 1e-3) / 1e9
+    traffic, tsrc = ncu_traffic(arm.cfg, arm.overflow, dom)
+    return {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": traffic, "traffic_source": tsrc,
+            "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": dom_bytes,
+            "touched": {"bytes_per_launch": k_touched.get(dom, 0), "achieved": achieved_t, "frac": achieved_t / peak,
+                        "points_processed": processed, "points_offered": arm.npts,
+                        "note": "break mode: k_insert stops handing out chunks of a frame once more than max_voxels "
+                                "cells are claimed; `touched` counts only the points it really read"},
+            "kernel_ms": per_kernel[dom], "kernel_share_of_step": per_kernel[dom] / ksum,
+            "per_kernel_ms": per_kernel,
+            "pipeline": {"algorithmic_bytes_per_step": pipe_bytes, "achieved": pipe_gbs, "frac": pipe_gbs / peak,
+                         "touched_bytes_per_step": pipe_touched,
+                         "frac_touched": pipe_touched / (ms_step * 1e-3) / 1e9 / peak}}
+
+
+def e2e_cfg4(args, pkg, torch, dev, arm, dist, world, total_pts, numa):
+    """End to end through generate_batched(pinned numpy): three DISTINCT pinned input batches in rotation (the
+    prefix guess of a call comes from other frames than the ones it is applied to), pinned outputs."""
+    c, B, T, cap = arm.c, arm.B, arm.T, arm.cap
+    hps = []
+    for fr in arm.host_sets:
+        cat = np.concatenate([f[0][0] for f in fr], axis=0)
+        hp = pkg.pinned_empty(cat.shape, np.float32)
+        hp[:] = cat
+        hps.append(hp)
+    hout = (pkg.pinned_empty((B * cap, T, 4), np.float32), pkg.pinned_empty((B * cap, 4), np.int32),
+            pkg.pinned_empty((B * cap,), np.int32), pkg.pinned_empty((B + 1,), np.int32))
+    ksteps = max(3, min(args.steps, 30))
+
+    def host_arm(prefix_upload, host_assemble=True):
+        gen_h = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=args.overflow,
+                                   device=dev, prefix_upload=prefix_upload, host_assemble=host_assemble)
+        gen_threads = gen_h._host_threads or min(32, len(os.sched_getaffinity(0)))
+        for i in range(3):
+            gen_h.generate_batched(hps[i % len(hps)], arm.offs, out=hout)
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        h2d = d2h = redone = 0
+        for i in range(ksteps):
+            gen_h.generate_batched(hps[i % len(hps)], arm.offs, out=hout)   # returns after the D2H completed
+            a, b_, rd = gen_h.last_transfer()                               # bytes the library actually copied
+            h2d += a; d2h += b_; redone += rd
+        dt = (time.perf_counter() - t0) / ksteps
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        gen_h.close()
+        return {"value": total_pts / dt / 1e6, "unit": UNIT, "ms_per_step": dt * 1e3, "steps": ksteps,
+                "h2d_bytes_per_step": h2d // ksteps, "d2h_bytes_per_step": d2h // ksteps,
+                "sub_batches_redone": redone, "input_batches_in_rotation": len(hps),
+                "api": "VoxelGenerator.generate_batched(numpy) -> bvx_generate_batched_host; pinned host "
+                       "buffers" + ("; break mode uploads only the prefix of each frame the cut-off can reach "
+                                    "(sized from the previous call, verified per frame, redone if short)"
+                                    if prefix_upload and args.overflow == "break" else "; whole frames uploaded")
+                       + ("; the kept rows come home compact (16 bytes per kept point), the zero padding is "
+                          "written by the handle's host threads" if host_assemble else
+                          "; padded rows gathered on the device and copied home"),
+                "host_threads": (gen_threads if host_assemble else 0),
+                "host_numa_binding": numa}
+
+    e2e = host_arm(True)
+    e2e_rows = host_arm(True, host_assemble=False)
+    e2e_full = host_arm(False, host_assemble=True) if args.overflow == "break" else None
+    return e2e, e2e_rows, e2e_full
+
+
+def e2e_single(args, pkg, torch, dev, arm, total_pts):
+    """End to end for the single-frame configs through the numpy forms of the public API (host arrays in,
+    host arrays out, a fresh call per step)."""
+    c = arm.c
+    gen_h = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], arm.T, arm.cap, overflow=args.overflow, device=dev)
+    ksteps = max(3, min(args.steps, 30))
+    sets = arm.host_sets
+
+    def one(i):
+        fr = sets[i % len(sets)]
+        if arm.cfg == "cfg3":
+            v, co, n, off = gen_h.generate_batched([f[0][0] for f in fr])
+            feat = pkg.VoxelFeatureExtractorV3()(torch.from_numpy(v).to(dev), torch.from_numpy(n).to(dev))
+            gx, gy, gz = (int(x) for x in gen_h.grid_size)
+            canvas = pkg.PointPillarsScatter([1, gz, gy, gx, 4])(feat, torch.from_numpy(co).to(dev), len(fr))
+            res = canvas.cpu().numpy()
+            return sum(f[0][0].nbytes for f in fr) + v.nbytes + n.nbytes + co.nbytes, v.nbytes + co.nbytes + n.nbytes + res.nbytes
+        if arm.sweeps:
+            if len(fr) == 1:
+                v, co, n = gen_h.generate_sweeps(fr[0])
+            else:
+                v, co, n, off = gen_h.generate_batched_sweeps(fr)
+            return sum(s[0].nbytes for f in fr for s in f), v.nbytes + co.nbytes + n.nbytes
+        if len(fr) == 1:
+            v, co, n = gen_h.generate(fr[0][0][0])
+        else:
+            v, co, n, off = gen_h.generate_batched([f[0][0] for f in fr])
+        return sum(f[0][0].nbytes for f in fr), v.nbytes + co.nbytes + n.nbytes
+
+    for i in range(3):
+        one(i)
+    t0 = time.perf_counter()
+    h2d = d2h = 0
+    for i in range(ksteps):
+        a, b = one(i)
+        h2d += a; d2h += b
+    dt = (time.perf_counter() - t0) / ksteps
+    gen_h.close()
+    api = {"cfg3": "generate_batched(numpy) + VoxelFeatureExtractorV3 + PointPillarsScatter, canvas read back",
+           "cfg2": "generate_sweeps(numpy sweeps)", "cfg5": "generate_sweeps(numpy sweeps)",
+           "cfg1": "generate(numpy)"}.get(arm.cfg, "generate_batched(numpy)")
+    return {"value": total_pts / dt / 1e6, "unit": UNIT, "ms_per_step": dt * 1e3, "steps": ksteps,
+            "h2d_bytes_per_step": h2d // ksteps, "d2h_bytes_per_step": d2h // ksteps,
+            "api": api + "; pageable numpy arrays in, numpy arrays out, synchronous"}
+
+
+def graph_replay(arm, steps):
+    """cfg1: the padded single-frame form as a CUDA graph (VoxelGenerator.capture), ms per replay, inputs rotated
+    by copying the next frame into the static buffer outside the timed replays."""
+    torch = arm.torch
+    if arm.cfg != "cfg1" or arm.B != 1:
+        return None
+    bufs = [d.clone() for d in arm.dsets]
+    graphs = [arm.gen.capture(b) for b in bufs]
+    for g, _ in graphs:
+        g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        graphs[i % len(graphs)][0].replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     pkg = importlib.import_module(PKG)
-    synth = pkg.synth
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -234,155 +571,120 @@ def run_ours(args):
     numa = None if args.no_numa_bind else pkg.shard.bind_host_to_device(local)   # before any pinned allocation
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    warmup = max(args.warmup, 3)
+    peak, peak_src = measured_peaks()
 
-    frames, c = build_frames(synth, rank, world, args.frames)
-    B, T, F, cap, C = len(frames), c["max_num_points"], 4, c["max_voxels"], 4
-    offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
-    npts = int(offs[-1])
-    host = np.concatenate(frames, axis=0)
-    # L2 hygiene: the timed steps rotate over NSETS distinct input batches (each 123 MB,
-    # together > the 126 MB L2); every step also writes ~128 MB of outputs.
-    NSETS = 3
-    sets = []
-    for k in range(NSETS):
-        order = np.roll(np.arange(B), -7 * k)
-        sets.append(torch.from_numpy(np.concatenate([frames[i] for i in order], axis=0)).to(dev))
-    gen = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=args.overflow, device=dev)
-    out = gen.generate_batched(sets[0], offs, mean_channels=C, padded=True)
-    torch.cuda.synchronize()
-    m_voxels = int(out[3][-1].item())
-    kept = int(out[2][:m_voxels].sum().item())
-
-    def step(i):
-        gen.generate_batched(sets[i % NSETS], offs, mean_channels=C, padded=True, out=out)
-
+    arm = Arm(args, pkg, torch, dev, rank, world)
+    arm.step(0)
+    m_voxels = arm.voxels()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    for i in range(max(args.warmup, 3)):
-        step(i)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    l0 = pkg._lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        step(i)
-    e1.record()
-    torch.cuda.synchronize()
-    launches = pkg._lib.launch_count() - l0
-    ms_total = e0.elapsed_time(e1)
-    if world > 1:
-        dist.barrier()
-        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-    ms_step = ms_total / args.steps
-    total_pts, total_vox = pkg.shard.gather_counts(npts, m_voxels) if world > 1 else (npts, m_voxels)
+    ms_step, launches = arm.time_steps(args.steps, warmup, dist, world)
+    total_pts, total_vox = pkg.shard.gather_counts(arm.npts, m_voxels) if world > 1 else (arm.npts, m_voxels)
     value = total_pts / (ms_step * 1e-3) / 1e6
+    per_kernel = arm.per_kernel(max(args.steps, 20))
+    roofline = roofline_block(arm, ms_step, per_kernel, m_voxels, peak, peak_src)
+    kept = None
+    if arm.cfg != "cfg3":
+        kept = int(arm.out[2][:m_voxels].sum().item())
 
-    # ---- per-kernel device times (CUDA events on the launching stream), same steps
-    gen.profile(True)
-    for i in range(args.steps):
-        step(i)
-    torch.cuda.synchronize()
-    prof = gen.profile_read()
-    gen.profile(False)
-    per_kernel = {k: v[0] / max(v[1], 1) for k, v in prof.items()}          # ms per launch
-    ksum = sum(per_kernel.values())
-    dom = max(per_kernel, key=per_kernel.get)
-    ab = algorithmic_bytes(npts, F, m_voxels, T, C)
-    # algorithmic bytes of each kernel = its share of the contract's compulsory I/O
-    k_bytes = {"k_insert": ab["points_in"],
-               "k_gather": ab["voxels_out"] + ab["coors_out"] + ab["num_out"] + ab["mean_out"]}
-    peak, peak_src = measured_peaks()
-    dom_bytes = k_bytes.get(dom, 0)
-    achieved = dom_bytes / (per_kernel[dom] * 1e-3) / 1e9
-    pipe_bytes = sum(ab.values())
-    pipe_gbs = pipe_bytes / (ms_step * 1e-3) / 1e9
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
-    # capture of this workload (profiles/r01_f_ncu_full_summary.txt); cold L2, cfg4 with 64 frames only
-    ncu_traffic = {"k_insert": 66.47e6 + 66.16e6, "k_verify": 1.05e6 + 0.00e6,
-                   "k_slot": 30.41e6 + 4.14e6, "k_gather": 74.95e6 + 96.87e6}
-    traffic = ncu_traffic.get(dom) if (B == 64 and args.overflow == "break") else None
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/r01_f_ncu_full_summary.txt (ncu --set full, cold L2)",
-                "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": dom_bytes,
-                "kernel_ms": per_kernel[dom], "kernel_share_of_step": per_kernel[dom] / ksum,
-                "per_kernel_ms": per_kernel,
-                "pipeline": {"algorithmic_bytes_per_step": pipe_bytes, "achieved": pipe_gbs,
-                             "frac": pipe_gbs / peak}}
+    extras = {}
+    if not args.no_extras:
+        # a longer timed region of the same step (the driver passes short --steps)
+        ms200, _ = arm.time_steps(200, 3, dist, world)
+        extras["steady_200_steps"] = {"ms_per_step": ms200, "value": total_pts / (ms200 * 1e-3) / 1e6}
+        g_ms = graph_replay(arm, 200)
+        if g_ms is not None:
+            extras["cuda_graph_replay"] = {"ms_per_step": g_ms, "value": arm.npts / (g_ms * 1e-3) / 1e6}
+        if arm.cfg == "cfg3":
+            # the three-call path as a user runs it: generate_batched (host sync for M) + VFE + scatter
+            vfe = pkg.VoxelFeatureExtractorV3()
+            gx, gy, gz = (int(x) for x in arm.gen.grid_size)
+            sc = pkg.PointPillarsScatter([1, gz, gy, gx, 4])
 
-    # ---- end to end through the host-buffer call: pinned numpy in, pinned numpy out
+            def three(i):
+                v, co, n, off = arm.gen.generate_batched(arm.dsets[i % arm.NSETS], arm.offs)
+                return sc(vfe(v, n), co, arm.B)
+            for i in range(3):
+                three(i)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(50):
+                three(i)
+            torch.cuda.synchronize()
+            ms3 = (time.perf_counter() - t0) / 50 * 1e3
+            ab3 = contract_bytes("cfg3", arm.npts, 4, 4, m_voxels, arm.T, 0)
+            b3 = sum(ab3.values()) + 4 * (m_voxels * arm.T * 4 + m_voxels + m_voxels * 4) + \
+                4 * (m_voxels * 4 + 4 * m_voxels + arm.B * 4 * gz * gy * gx)
+            extras["three_call_path"] = {"ms_per_step": ms3, "value": arm.npts / (ms3 * 1e-3) / 1e6,
+                                         "algorithmic_bytes_per_step": b3,
+                                         "frac": b3 / (ms3 * 1e-3) / 1e9 / peak,
+                                         "api": "generate_batched (sync for M) + VoxelFeatureExtractorV3 + PointPillarsScatter"}
+        if arm.B == 1 and arm.cfg != "cfg4":
+            # (iii) a 64-frame batch of the same shape
+            a64 = Arm(args, pkg, torch, dev, rank, world, frames=64)
+            a64.step(0)
+            m64 = a64.voxels()
+            ms64, _ = a64.time_steps(50, 3, dist, world)
+            ab64 = sum(a64.bytes(m64).values())
+            extras["batch_of_64"] = {"ms_per_step": ms64, "value": a64.npts / (ms64 * 1e-3) / 1e6,
+                                     "algorithmic_bytes_per_step": ab64, "frac": ab64 / (ms64 * 1e-3) / 1e9 / peak,
+                                     "voxels": m64}
+            a64.close()
+        if args.overflow == "break":
+            # the same workload with overflow=continue: every offered byte really is read
+            ac = Arm(args, pkg, torch, dev, rank, world, overflow="continue")
+            ac.step(0)
+            mc = ac.voxels()
+            msc, _ = ac.time_steps(max(20, min(args.steps, 100)), 3, dist, world)
+            pkc = ac.per_kernel(20)
+            rc = roofline_block(ac, msc, pkc, mc, peak, peak_src)
+            extras["continue_mode"] = {"ms_per_step": msc, "value": total_pts / (msc * 1e-3) / 1e6, "voxels": mc,
+                                       "roofline": rc}
+            ac.close()
+        if world > 1 and arm.cfg == "cfg4" and args.scaling == "weak":
+            # the literal BASELINE cfg4: 64 frames in total, 64 / N per rank
+            a_s = Arm(args, pkg, torch, dev, rank, world, frames=max(1, 64 // world))
+            a_s.step(0)
+            a_s.voxels()
+            ms_s, _ = a_s.time_steps(max(20, min(args.steps, 100)), 3, dist, world)
+            pts_s, _ = pkg.shard.gather_counts(a_s.npts, 0)
+            extras["strong_scaling_64_frames_total"] = {"frames_per_gpu": a_s.B, "ms_per_step": ms_s,
+                                                        "value": pts_s / (ms_s * 1e-3) / 1e6}
+            a_s.close()
+
+    # ---- end to end through the host-buffer calls
     e2e = e2e_full = e2e_rows = None
     if not args.no_e2e:
-        hp = pkg.pinned_empty(host.shape, np.float32)
-        hp[:] = host
-        hout = (pkg.pinned_empty((B * cap, T, F), np.float32), pkg.pinned_empty((B * cap, 4), np.int32),
-                pkg.pinned_empty((B * cap,), np.int32), pkg.pinned_empty((B + 1,), np.int32))
-        ksteps = max(3, min(args.steps, 20))
-
-        def host_arm(prefix_upload, host_assemble=True):
-            gen_h = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=args.overflow,
-                                       device=dev, prefix_upload=prefix_upload, host_assemble=host_assemble)
-            gen_threads = gen_h._host_threads or min(32, len(os.sched_getaffinity(0)))
-            for _ in range(3):
-                r = gen_h.generate_batched(hp, offs, out=hout)
-            if world > 1:
-                dist.barrier()
-            t0 = time.perf_counter()
-            h2d = d2h = redone = 0
-            for _ in range(ksteps):
-                r = gen_h.generate_batched(hp, offs, out=hout)      # returns after the D2H completed
-                a, b_, rd = gen_h.last_transfer()                   # bytes the library actually copied
-                h2d += a; d2h += b_; redone += rd
-            dt = (time.perf_counter() - t0) / ksteps
-            if world > 1:
-                t = torch.tensor([dt], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                dt = float(t.item())
-            gen_h.close()
-            return {"value": total_pts / dt / 1e6, "unit": UNIT, "ms_per_step": dt * 1e3, "steps": ksteps,
-                    "h2d_bytes_per_step": h2d // ksteps, "d2h_bytes_per_step": d2h // ksteps,
-                    "sub_batches_redone": redone,
-                    "api": "VoxelGenerator.generate_batched(numpy) -> bvx_generate_batched_host; pinned host "
-                           "buffers" + ("; break mode uploads only the prefix of each frame the cut-off can reach "
-                                        "(sized from the previous call, verified per frame, redone if short)"
-                                        if prefix_upload and args.overflow == "break" else "; whole frames uploaded")
-                           + ("; the kept rows come home compact (16 bytes per kept point), the zero padding is "
-                              "written by the handle's host threads" if host_assemble else
-                              "; padded rows gathered on the device and copied home"),
-                    "host_threads": (gen_threads if host_assemble else 0),
-                    "host_numa_binding": numa}
-
-        e2e = host_arm(True)
-        e2e_rows = host_arm(True, host_assemble=False)
-        if args.overflow == "break":
-            e2e_full = host_arm(False, host_assemble=False)
+        if arm.cfg == "cfg4":
+            e2e, e2e_rows, e2e_full = e2e_cfg4(args, pkg, torch, dev, arm, dist, world, total_pts, numa)
+        else:
+            e2e = e2e_single(args, pkg, torch, dev, arm, arm.npts)
     clocks = sampler.stop() if rank == 0 else None
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, done = cpu_oracle_single_core(frames, c, args.overflow)
+        v, done = cpu_oracle_single_core(arm.host_sets[0], arm.c, args.overflow, arm.cfg)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": f"{done} points ({done // npts} passes over the same {B} frames), C oracle kernel only "
-                         "(dense grid cached and reset, outputs pre-allocated)"}
+               "sample": f"{done} points ({done // arm.npts} passes over the same {arm.B} frame(s)), C oracle kernel only "
+                         "(dense grid cached and reset, outputs pre-allocated)"
+                         + (" + mean VFE + BEV scatter" if arm.cfg == "cfg3" else "")}
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "frames_per_gpu": B, "points_per_gpu": npts,
-                           "voxels_per_gpu": m_voxels, "kept_points_per_gpu": kept, "overflow": args.overflow,
-                           "l2": f"inputs rotate over {NSETS} distinct {host.nbytes >> 20} MiB batches "
-                                 "(> 126 MB L2); outputs rewritten every step; no explicit flush"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_device_rows": e2e_rows, "e2e_full_upload": e2e_full,
-                "gpu_launches": int(launches),
-                "clocks": clocks}
+                "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": config_dict(args, world),
+                "workload_detail": {"points_per_gpu": arm.npts, "voxels_per_gpu": m_voxels,
+                                    "kept_points_per_gpu": kept, "input_mib_per_batch": arm.input_bytes >> 20,
+                                    "value_counts": "points offered to the call (before range filtering and the "
+                                                    "break cut-off); roofline.touched has the points processed"},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "e2e_device_rows": e2e_rows, "e2e_full_upload": e2e_full,
+                "gpu_launches": int(launches), "clocks": clocks}
+        line.update(extras)
         print(json.dumps(line))
+    arm.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

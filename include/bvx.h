@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BVX_ABI_VERSION 2
+#define BVX_ABI_VERSION 3
 
 typedef enum bvx_status {
     BVX_OK = 0,
@@ -246,6 +246,21 @@ int bvx_host_assemble_compact(const float* rows, const int32_t* tile_base,
                               float* voxels, int32_t threads);
 int bvx_last_transfer(const bvx_handle* h, uint64_t* h2d_bytes,
                       uint64_t* d2h_bytes, int32_t* redone);
+
+/* Per-frame facts of the last device- or host-form call on the handle (frames
+ * 0 .. b-1 of that call; for the pipelined host form: of its last sub-batch),
+ * copied to HOST arrays (each may be NULL); synchronises the stream.
+ *   cells     distinct in-range cells among the points that were looked at
+ *   voxels    M_b = min(cells, max_voxels)
+ *   cutoff    BREAK mode, cells > max_voxels: index of the point that would have
+ *             opened voxel number max_voxels (the reference's loop stops there);
+ *             else = processed
+ *   processed points of the frame that went through the insert kernel: in BREAK
+ *             mode the kernel stops handing out chunks of a frame once more than
+ *             max_voxels cells are claimed, so this is a prefix of the frame.
+ *             bench.py uses it for the "bytes actually read" roofline figure. */
+int bvx_frame_stats(bvx_handle* h, int32_t b, int32_t* cells, int32_t* voxels,
+                    int32_t* cutoff, int32_t* processed, void* stream);
 
 /* Replaces VoxelFeatureExtractorV3.forward(features, num_voxels)
  * (second/pytorch/models/voxel_encoder.py:201-206): out[v, c] =

@@ -557,43 +557,128 @@ def test_full_size_single_frame_configs(pkg, oracle, synth, name, overflow):
 
 
 @pytest.mark.parametrize("name", ["cfg2", "cfg5"])
-def test_full_size_sweep_configs(pkg, oracle, synth, name):
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_full_size_sweep_configs(pkg, oracle, synth, name, overflow):
+    """cfg2 (5 sweeps, T=10) and cfg5 (3 x 180k points, 150k-voxel cap: with `continue` every one of the
+    540k points goes through the hashed table) at full size, both overflow rules."""
     c = synth.CONFIGS[name]
     sweeps = synth.make_sweeps(name)
-    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"])
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"],
+                           overflow=overflow)
     o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
-                                    c["max_voxels"])
+                                    c["max_voxels"], overflow=overflow)
     dsw = [(torch.from_numpy(p).cuda(), R, t, dt) for p, R, t, dt in sweeps]
-    _eq(g.generate_sweeps(dsw), o.generate(oracle.merge_sweeps(sweeps)), name)
+    want = o.generate(oracle.merge_sweeps(sweeps))
+    _eq(g.generate_sweeps(dsw), want, name)
+    _eq(g.generate_sweeps(dsw), want, name + " second call")
 
 
-def test_full_size_cfg4_batch_properties(pkg, oracle, synth):
-    """BASELINE cfg4 (64 x 120k): full oracle comparison on 8 frames, size-independent
-    properties on all 64 (per-frame results identical to single-frame calls, sorted
-    offsets, counts in [1, T], every kept point inside its voxel)."""
+def _cfg4_oracle(oracle, synth, overflow):
     c = synth.CONFIGS["cfg4"]
     frames = synth.make_frames("cfg4", 64)
-    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"])
     o = oracle.OracleVoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"],
-                                    c["max_voxels"])
-    dframes = [torch.from_numpy(f).cuda() for f in frames]
-    v, cc, n, off = g.generate_batched(dframes)
-    off = off.cpu().numpy()
+                                    c["max_voxels"], overflow=overflow)
+    return c, frames, o.generate_batched(frames)
+
+
+_CFG4_CACHE = {}
+
+
+def _cfg4(oracle, synth, overflow):
+    if overflow not in _CFG4_CACHE:
+        _CFG4_CACHE[overflow] = _cfg4_oracle(oracle, synth, overflow)
+    return _CFG4_CACHE[overflow]
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_full_size_cfg4_device_form(pkg, oracle, synth, overflow):
+    """BASELINE cfg4 (64 x 120k points), the batch bench.py times on the device: ALL 64 frames against the
+    oracle, both overflow rules, fused mean VFE included, twice on one handle; plus size-independent
+    properties (sorted offsets, counts in [1, T], every kept point inside its voxel, zero padding)."""
+    c, frames, want = _cfg4(oracle, synth, overflow)
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"],
+                           overflow=overflow)
+    cat = torch.from_numpy(np.concatenate(frames)).cuda()
+    offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
+    for call in range(2):
+        v, cc, n, off, mean = g.generate_batched(cat, offs, mean_channels=4)
+        assert np.array_equal(off.cpu().numpy(), want[3]), f"offsets, call {call}"
+        _eq((v, cc, n), want[:3], f"cfg4 device form {overflow}, call {call}")
+        np.testing.assert_allclose(mean.cpu().numpy(), oracle.mean_vfe(want[0], want[2]), rtol=1e-6, atol=0)
+    off = want[3]
     assert off[0] == 0 and np.all(np.diff(off) == c["max_voxels"])   # the cap is hit in every frame
     vn, cn, nn = v.cpu().numpy(), cc.cpu().numpy(), n.cpu().numpy()
     assert nn.min() >= 1 and nn.max() <= c["max_num_points"]
-    for b in range(0, 64, 8):
-        wv, wc, wn = o.generate(frames[b])
-        sl = slice(off[b], off[b + 1])
-        assert np.all(cn[sl, 0] == b)
-        _eq((vn[sl], cn[sl, 1:], nn[sl]), (wv, wc, wn), f"cfg4 frame {b}")
-    # every kept point lies inside the voxel it was assigned to
+    assert np.array_equal(cn[:, 0], np.repeat(np.arange(64), c["max_voxels"]))
     vs = np.asarray(c["voxel_size"], np.float32)
     lo = np.asarray(c["point_cloud_range"][:3], np.float32)
     slot = np.arange(c["max_num_points"])[None, :] < nn[:, None]
     cell = np.floor((vn[..., :3] - lo) / vs).astype(np.int32)[..., ::-1]
     assert np.all((cell == cn[:, None, 1:])[slot])
     assert np.all(vn[~slot] == 0)
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+@pytest.mark.parametrize("prefix_upload,host_assemble", [(True, True), (True, False), (False, True), (False, False)])
+def test_full_size_cfg4_host_form(pkg, oracle, synth, overflow, prefix_upload, host_assemble):
+    """The path bench.py's end-to-end figure runs -- generate_batched(pinned numpy) at 64 x 120k points:
+    prefix upload x host assembly on and off, both overflow rules, all 64 frames against the oracle.  Three
+    calls on one handle: the first uploads whole frames, the second works from the guessed prefix, the
+    third gets the frames in another order (its guess comes from different frames)."""
+    c, frames, want = _cfg4(oracle, synth, overflow)
+    cap, T = c["max_voxels"], c["max_num_points"]
+    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, overflow=overflow,
+                           prefix_upload=prefix_upload, host_assemble=host_assemble)
+    hp, offs, out = _pinned_batch(pkg, frames, cap, T)
+    for call in range(2):
+        hv, hc, hn, hoff = g.generate_batched(hp, offs, out=out)
+        assert np.array_equal(hoff, want[3])
+        _eq((hv, hc, hn), want[:3], f"cfg4 host form {overflow} prefix={prefix_upload} assemble={host_assemble} call {call}")
+        h2d, d2h, redone = g.last_transfer()
+        if call == 1 and overflow == "break" and prefix_upload:
+            assert h2d < 0.8 * hp.nbytes and redone == 0          # the guess held: a prefix was enough
+        if call == 0 or overflow == "continue" or not prefix_upload:
+            assert h2d == hp.nbytes
+    order = np.roll(np.arange(64), -17)
+    hp2, offs2, out2 = _pinned_batch(pkg, [frames[i] for i in order], cap, T)
+    hv, hc, hn, hoff = g.generate_batched(hp2, offs2, out=out2)
+    o = want[3]
+    for k, i in enumerate(order):                                   # frame k of this call is frame i of the oracle's
+        a, b = hoff[k], hoff[k + 1]
+        assert b - a == o[i + 1] - o[i]
+        assert np.all(hc[a:b, 0] == k)
+        _eq((hv[a:b], hc[a:b, 1:], hn[a:b]), (want[0][o[i]:o[i + 1]], want[1][o[i]:o[i + 1], 1:], want[2][o[i]:o[i + 1]]),
+            f"rotated batch, frame {k}")
+
+
+def test_table_load_factor_worst_case(pkg, oracle):
+    """N = 2^k - 1 points, every one in a cell of its own, continue mode with a cap above N: the hashed table is
+    sized so that its load factor stays below 11/12 (it was N / 2^k ~ 1.0, i.e. O(N) probes per point)."""
+    n = (1 << 14) - 1
+    grid = dict(voxel_size=[1.0, 1.0, 1.0], point_cloud_range=[0, 0, 0, 128, 128, 1])
+    ij = np.arange(n)
+    pts = np.stack([ij % 128 + 0.5, ij // 128 + 0.5, np.full(n, 0.5), np.zeros(n)], axis=1).astype(np.float32)
+    pts = pts[np.random.default_rng(0).permutation(n)]
+    for overflow in ("continue", "break"):
+        g, o = _pair(pkg, oracle, grid, 3, 20000, overflow)
+        _eq(g.generate(torch.from_numpy(pts).cuda()), o.generate(pts), f"all distinct, {overflow}")
+
+
+def test_big_frame_scan_path(pkg, oracle, synth, monkeypatch):
+    """Frames of more than 4096 chunks (> 4 M points) scan their chunk counts in a kernel of their own
+    (k_scan_big) instead of in shared memory; the limit is lowered through BVX_SCAN_SMEM_CHUNKS so that the
+    path runs on a small frame: same results."""
+    monkeypatch.setenv("BVX_SCAN_SMEM_CHUNKS", "4")
+    frames = [synth.lidar_frame(n, "kitti", seed=900 + i) for i, n in enumerate([30000, 5000, 0, 21000])]
+    for overflow in ("break", "continue"):
+        for T, cap in ((5, 1500), (12, 900), (1, 100000)):
+            g, o = _pair(pkg, oracle, KITTI, T, cap, overflow)
+            want = o.generate_batched(frames)
+            for _ in range(2):
+                got = g.generate_batched([torch.from_numpy(f).cuda() for f in frames])
+                assert np.array_equal(got[3].cpu().numpy(), want[3])
+                _eq(got[:3], want[:3], f"big-frame path T={T} cap={cap} {overflow}")
+            g.close()
 
 
 def test_mean_vfe_and_scatter_golden(pkg, oracle, golden_dir):
@@ -688,6 +773,9 @@ def test_cuda_graph_replay(pkg, oracle, synth, overflow):
         torch.cuda.synchronize()
         m = int(cnt.item())
         _eq((v[:m], c[:m], n[:m]), o.generate(f), "graph replay, single frame")
+        # a plain call of another size on the same generator in between must not disturb the graph
+        other = synth.lidar_frame(7000 + 1000 * m % 3000, "kitti", seed=77)
+        _eq(g.generate(torch.from_numpy(other).cuda()), o.generate(other), "plain call between replays")
     # batched, out= buffers, fused mean
     cat = torch.empty((3 * 20000, 4), dtype=torch.float32, device="cuda")
     offs = np.asarray([0, 20000, 40000, 60000], np.int32)
