@@ -40,9 +40,6 @@ constexpr int kWarps = kBlock / 32;
 constexpr int kUnit = 32 * kPts;     // 128 points: what one warp owns of a chunk
 constexpr int kScanSmemChunks = 4096;  // frames up to this many chunks are scanned in shared memory by k_mid
 constexpr int kInlineFrames = 64;      // calls of up to this many frames carry their frame descriptors as kernel arguments
-#ifndef BVX_ABL
-#define BVX_ABL 0   // timing ablations of experiment builds (tools/variants.sh); 0 in the product
-#endif
 #ifndef BVX_GATHER_PF
 #define BVX_GATHER_PF 0
 #endif
@@ -790,19 +787,6 @@ __device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, in
     int r1 = v1 ? extra_rank<BIG>(p, fr, e1, s_pre, s_lost) : 0x7FFFFFFF;
     const bool chain = p.T <= kChainMaxT;
     int o0 = 0, o1 = 0;
-#if BVX_ABL == 5
-    if (r0 + r1 == -12345) p.vfirst[0] = 1;
-    return;
-#endif
-#if BVX_ABL == 6
-    if (chain) {
-        const int T1 = p.T - 1;
-        if ((unsigned)r0 < (unsigned)p.cap) o0 = p.bucket[((size_t)f * p.cap + r0) * T1];
-        if ((unsigned)r1 < (unsigned)p.cap) o1 = p.bucket[((size_t)f * p.cap + r1) * T1];
-        if (o0 + o1 == -12345) p.vfirst[0] = 1;
-        return;
-    }
-#endif
     if (chain) {
         const int T1 = p.T - 1;
         if ((unsigned)r0 < (unsigned)p.cap) o0 = atomicMin(p.bucket + ((size_t)f * p.cap + r0) * T1, e0.x);
@@ -846,9 +830,6 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
     const bool role2 = n2 == 0 || (int)blockIdx.x < n2, role3 = (n2 == 0 || (int)blockIdx.x >= n2) && !publisher;
     const int nw2 = (n2 == 0 ? gx : n2) * kWarps, nw3 = (n2 == 0 ? gx : gx - n2) * kWarps;
     const int w2 = blockIdx.x * kWarps + wid, w3 = (n2 == 0 ? (int)blockIdx.x : (int)blockIdx.x - n2) * kWarps + wid;
-#if BVX_ABL == 3
-    if (!publisher) return;
-#endif
     // the bitmap words of the first chunk this warp numbers are fetched before anything else
     unsigned int pf_c = 0, pf_l = 0;
     if (!BIG && role2 && !publisher && w2 < fr.nchunks) {
@@ -906,9 +887,6 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
             return;
         }
     }
-#if BVX_ABL == 4
-    return;
-#endif
     const int nwords = (eff + 31) / 32;
     const int nlim = (brk && total > cap) ? cut_chunk + 1 : nch;   // chunks that can hold anything that is kept
     if (role2) {
@@ -963,9 +941,6 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
         }
     }
     if (BIG || p.T <= 1 || !role3) return;
-#if BVX_ABL == 1
-    return;
-#endif
     // extras of chunks [0, nlim), flattened: item g of the frame belongs to the chunk c with
     // s_epre[c] <= g < s_epre[c + 1]; consecutive lanes take consecutive items, two per lane at a time
     const int E = s_epre[nlim];
@@ -1103,36 +1078,48 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
     pdl_prologue();
     const int f = blockIdx.y;
     const FrameDesc fr = frame_desc(p, f);
-    tidy_frame(p, fr, f);
-    if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
-    const int mf = p.state[f].m;
+    if ((int)blockIdx.x >= tiles) { tidy_frame(p, fr, f); reset_chunk(p, fr, blockIdx.x - tiles); return; }
     const int v0 = blockIdx.x * kBlock;
-    if (v0 >= mf) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int v = v0 + threadIdx.x;
-    const bool live = v < mf;
+    // The point indices of the voxel are fetched BEFORE the frame's voxel count is known (their addresses
+    // do not depend on it; rows behind the count hold nothing that is used): the block's chain of
+    // dependent round trips is indices -> rows -> stores, not count -> indices -> rows -> stores.
+    int raw0 = kEmptyIdx;
+    int rawx[T > 1 ? T - 1 : 1];
+    int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
+    if (v < p.cap) {
+        raw0 = __ldcs(p.vfirst + (size_t)f * p.cap + v);
+        if (T == 5) {
+            const int4 e = *reinterpret_cast<const int4*>(gb);
+            rawx[0] = e.x; rawx[1 % (T > 1 ? T - 1 : 1)] = e.y; rawx[2 % (T > 1 ? T - 1 : 1)] = e.z; rawx[3 % (T > 1 ? T - 1 : 1)] = e.w;
+        } else {
+#pragma unroll
+            for (int s = 1; s < T; ++s) rawx[s - 1] = gb[s - 1];
+        }
+    } else {
+#pragma unroll
+        for (int s = 1; s < T; ++s) rawx[s - 1] = kEmptyIdx;
+    }
+    const int mf = p.state[f].m;
+    const int istar = p.state[f].istar;
     const size_t gbase = (size_t)p.frame_voxel_offsets[f];
+    if (v0 >= mf) { tidy_frame(p, fr, f); return; }
+    const bool live = v < mf;
     int idx[T];
-    idx[0] = live ? __ldcs(p.vfirst + (size_t)f * p.cap + v) : kEmptyIdx;
+    idx[0] = live ? raw0 : kEmptyIdx;
     if (T > 1) {
         // the voxel's other points, ascending; a row that held any is put back to empty for the next
         // call.  Break mode: entries behind the cut-off i* (a suffix of the row) are dropped here.
-        const int istar = p.state[f].istar;
-        int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
         if (T == 5) {
-            int4 e = make_int4(kEmptyIdx, kEmptyIdx, kEmptyIdx, kEmptyIdx);
-            if (live) e = *reinterpret_cast<const int4*>(gb);
-            if (e.x != kEmptyIdx)
+            if (live && rawx[0] != kEmptyIdx)
                 *reinterpret_cast<int4*>(gb) = make_int4(kEmptyIdx, kEmptyIdx, kEmptyIdx, kEmptyIdx);
-            idx[1 % T] = e.x < istar ? e.x : kEmptyIdx; idx[2 % T] = e.y < istar ? e.y : kEmptyIdx;
-            idx[3 % T] = e.z < istar ? e.z : kEmptyIdx; idx[4 % T] = e.w < istar ? e.w : kEmptyIdx;
-        } else {
+        }
 #pragma unroll
-            for (int s = 1; s < T; ++s) {
-                const int raw = live ? gb[s - 1] : kEmptyIdx;
-                if (raw != kEmptyIdx) gb[s - 1] = kEmptyIdx;
-                idx[s] = raw < istar ? raw : kEmptyIdx;
-            }
+        for (int s = 1; s < T; ++s) {
+            const int raw = live ? rawx[s - 1] : kEmptyIdx;
+            if (T != 5 && raw != kEmptyIdx) gb[s - 1] = kEmptyIdx;
+            idx[s] = raw < istar ? raw : kEmptyIdx;
         }
     }
     const float4* rows = reinterpret_cast<const float4*>(plain_rows(p, fr));
@@ -1184,6 +1171,7 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
         for (int s = 0; s < T; ++s)
             if (s < nvalid) __stcs(dst + s, own(s));
     }
+    tidy_frame(p, fr, f);        // last: nothing of this block waits for it
     if (!live) return;
     const size_t gv = gbase + v;
     if (p.idx_out) {
