@@ -16,7 +16,9 @@ from .shard import shard_frames  # noqa: F401
 def __getattr__(name):
     # torch-dependent pieces are imported on first use
     if name in ("VoxelFeatureExtractorV3", "SimpleVoxel", "PointPillarsScatter", "mean_vfe",
-                "scatter_bev", "VFE_CLASS_DICT", "MIDDLE_CLASS_DICT", "modules"):
+                "scatter_bev", "VFE_CLASS_DICT", "MIDDLE_CLASS_DICT", "modules", "VFELayer",
+                "VoxelFeatureExtractor", "VoxelFeatureExtractorV2", "get_paddings_indicator", "vfe_augment",
+                "masked_max", "scatter_index_bev"):
         import importlib
         mod = importlib.import_module(__name__ + ".modules")
         return mod if name == "modules" else getattr(mod, name)

@@ -1526,6 +1526,7 @@ extern "C" int bvx_scatter_bev_dev(const float* feats, const int32_t* coors4, co
 struct ScatterMap { int dev; cudaStream_t st; int* p; size_t count; };
 static std::mutex g_map_mu;
 static std::vector<ScatterMap> g_maps;
+static int* scatter_map(cudaStream_t st, size_t cells);
 
 static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, const int32_t* m_dev, int32_t c,
                        int32_t b, int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream)
@@ -1544,26 +1545,8 @@ static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, con
         k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(canvas), n4, canvas + (n4 << 2), (int)(total & 3));
         g_launches += 1;
     } else {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        int* map = nullptr;
-        {
-            std::lock_guard<std::mutex> lk(g_map_mu);
-            ScatterMap* sm = nullptr;
-            for (ScatterMap& e : g_maps)
-                if (e.dev == dev && e.st == st) sm = &e;
-            if (!sm) {
-                g_maps.push_back(ScatterMap{dev, st, nullptr, 0});
-                sm = &g_maps.back();
-            }
-            if (sm->count < cells + 4) {
-                if (sm->p) { cudaStreamSynchronize(st); cudaFree(sm->p); sm->p = nullptr; sm->count = 0; }
-                cudaError_t e = cudaMalloc((void**)&sm->p, (cells + 4) * sizeof(int));
-                if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "scatter map: %s", cudaGetErrorString(e));
-                sm->count = cells + 4;
-            }
-            map = sm->p;
-        }
+        int* map = scatter_map(st, cells);
+        if (!map) return fail(nullptr, BVX_ERR_CUDA, "scatter: cannot allocate the map");
         k_bev_map<<<(m + kBlock - 1) / kBlock, kBlock, 0, st>>>(reinterpret_cast<const int4*>(coors4), m, m_dev, b, d, ny, nx, map);
         // channel slices: enough blocks to fill the GPU, at most 8 channels per thread
         const bool vec = (nx & 3) == 0;
@@ -1582,6 +1565,97 @@ static int scatter_bev(const float* feats, const int32_t* coors4, int32_t m, con
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "scatter launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+static int* scatter_map(cudaStream_t st, size_t cells)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    ScatterMap* sm = nullptr;
+    for (ScatterMap& e : g_maps)
+        if (e.dev == dev && e.st == st) sm = &e;
+    if (!sm) {
+        g_maps.push_back(ScatterMap{dev, st, nullptr, 0});
+        sm = &g_maps.back();
+    }
+    if (sm->count < cells + 4) {
+        if (sm->p) { cudaStreamSynchronize(st); cudaFree(sm->p); sm->p = nullptr; sm->count = 0; }
+        if (cudaMalloc((void**)&sm->p, (cells + 4) * sizeof(int)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        sm->count = cells + 4;
+    }
+    return sm->p;
+}
+
+extern "C" int bvx_scatter_index_bev(const float* src, int32_t b, int32_t c, int32_t s0, int32_t s1,
+                                     const int32_t* src_idx, const int32_t* dst_xy, int32_t np, int32_t ny,
+                                     int32_t nx, float* out, void* stream)
+{
+    if (b < 1 || c < 1 || s0 < 1 || s1 < 1 || np < 0 || ny < 1 || nx < 1)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad index-scatter shape");
+    if (!out || (np > 0 && (!src || !dst_xy))) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    if (((uintptr_t)out & 15) || ((uintptr_t)dst_xy & 7) || ((uintptr_t)src_idx & 7))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "out must be 16-byte aligned, the index arrays 8-byte aligned");
+    if (!src_idx && (long long)np > (long long)s0 * s1)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "implicit source mesh: np must be <= s0 * s1");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cells = (size_t)b * ny * nx;
+    int* map = scatter_map(st, cells);
+    if (!map) return fail(nullptr, BVX_ERR_CUDA, "index scatter: cannot allocate the map");
+    k_fill_i32<<<(int)std::min<size_t>((cells + kBlock - 1) / kBlock, 148 * 8), kBlock, 0, st>>>(map, cells, -1);
+    g_launches += 1;
+    if (np > 0) {
+        const long long work = (long long)b * np;
+        k_idx_map<<<(unsigned)((work + kBlock - 1) / kBlock), kBlock, 0, st>>>(reinterpret_cast<const int2*>(dst_xy), b, np, ny, nx, map);
+        g_launches += 1;
+    }
+    const bool vec = (nx & 3) == 0;
+    const long long groups = (long long)(cells / (vec ? 4 : 1));
+    const int gb = (int)((groups + kBlock - 1) / kBlock);
+    int ch_per = c;
+    while (ch_per > 8 || (ch_per > 1 && (long long)gb * ((c + ch_per - 1) / ch_per) < 148 * 8)) ch_per = (ch_per + 1) / 2;
+    const dim3 grid(gb, (c + ch_per - 1) / ch_per);
+    if (vec) k_idx_canvas<4><<<grid, kBlock, 0, st>>>(src, reinterpret_cast<const int2*>(src_idx), c, b, s0, s1, ny, nx, map, out, ch_per);
+    else k_idx_canvas<1><<<grid, kBlock, 0, st>>>(src, reinterpret_cast<const int2*>(src_idx), c, b, s0, s1, ny, nx, map, out, ch_per);
+    g_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "index scatter launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+extern "C" int bvx_vfe_augment(const float* voxels, const int32_t* num_points, int32_t m, int32_t t, int32_t f,
+                               int32_t with_distance, float* out, float* mask, void* stream)
+{
+    if (m < 0 || t < 1 || f < 3) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad vfe_augment shape m=%d t=%d f=%d", m, t, f);
+    if (m == 0) return BVX_OK;
+    if (!voxels || !num_points || !out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    int vt = std::max(1, std::min(64, 8192 / (t * f)));
+    const size_t smem = ((size_t)vt * t * f + (size_t)vt * 3) * 4;
+    if (smem > 200 * 1024) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "t*f too large for the VFE tile");
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_vfe_augment, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
+    k_vfe_augment<<<(m + vt - 1) / vt, kBlock, smem, (cudaStream_t)stream>>>(voxels, num_points, m, t, f, with_distance ? 1 : 0,
+                                                                             vt, out, mask);
+    g_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "k_vfe_augment launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
+extern "C" int bvx_masked_max(const float* x, const int32_t* num_points, int32_t m, int32_t t, int32_t c, float* out,
+                              int32_t* argmax, void* stream)
+{
+    if (m < 0 || t < 1 || c < 1) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad masked_max shape");
+    if (m == 0) return BVX_OK;
+    if (!x || !num_points || !out) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    const long long work = (long long)m * c;
+    k_masked_max<<<(unsigned)((work + kBlock - 1) / kBlock), kBlock, 0, (cudaStream_t)stream>>>(x, num_points, m, t, c, out, argmax);
+    g_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "k_masked_max launch: %s", cudaGetErrorString(e));
     return BVX_OK;
 }
 

@@ -1434,4 +1434,135 @@ __global__ void __launch_bounds__(kBlock) k_bev_canvas(const float* __restrict__
     }
 }
 
+// ---------------------------------------------------------------- learned VFE: the bandwidth part
+// VoxelFeatureExtractor / V2 (second/pytorch/models/voxel_encoder.py:100-112, 165-176) before their first
+// linear layer: points_mean = sum_t xyz / num; features = cat([features, xyz - points_mean (, |xyz|_2)]),
+// for ALL T slots (the reference does not mask its input: a padded slot gets -points_mean), and the
+// padding indicator mask[v, t] = t < num[v] (get_paddings_indicator, voxel_encoder.py:12-33) as floats.
+// A tile of vt voxels is staged in shared memory so that both the [M, T, F] read and the [M, T, Fo] write
+// are fully coalesced.  dynamic smem: vt * (T * F + 3) floats.
+__global__ void __launch_bounds__(kBlock) k_vfe_augment(const float* __restrict__ voxels, const int* __restrict__ num,
+                                                        int m, int T, int F, int with_distance, int vt,
+                                                        float* __restrict__ out, float* __restrict__ mask)
+{
+    extern __shared__ float smem_f[];
+    float* smean = smem_f + (size_t)vt * T * F;
+    const int v0 = blockIdx.x * vt;
+    if (v0 >= m) return;
+    const int nv = min(vt, m - v0);
+    const size_t base = (size_t)v0 * T * F;
+    const int tot = nv * T * F;
+    if ((tot & 3) == 0 && (base & 3) == 0) {
+        const float4* g4 = reinterpret_cast<const float4*>(voxels + base);
+        float4* s4 = reinterpret_cast<float4*>(smem_f);
+        for (int k = threadIdx.x; k < (tot >> 2); k += kBlock) s4[k] = __ldg(g4 + k);
+    } else {
+        for (int k = threadIdx.x; k < tot; k += kBlock) smem_f[k] = __ldg(voxels + base + k);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < nv * 3; k += kBlock) {
+        const int v = k / 3, c = k - v * 3;
+        float s = 0.0f;
+        for (int j = 0; j < T; ++j) s = __fadd_rn(s, smem_f[(size_t)(v * T + j) * F + c]);
+        smean[k] = __fdiv_rn(s, (float)num[v0 + v]);
+    }
+    __syncthreads();
+    const int Fo = F + 3 + (with_distance ? 1 : 0);
+    float* o = out + (size_t)v0 * T * Fo;
+    for (int k = threadIdx.x; k < nv * T * Fo; k += kBlock) {
+        const int row = k / Fo, c = k - row * Fo;            // row = v * T + t
+        const float* in = smem_f + (size_t)row * F;
+        float r;
+        if (c < F) r = in[c];
+        else if (c < F + 3) r = __fsub_rn(in[c - F], smean[(row / T) * 3 + (c - F)]);
+        else r = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(in[0], in[0]), __fmul_rn(in[1], in[1])), __fmul_rn(in[2], in[2])));
+        o[k] = r;
+    }
+    if (mask) {
+        for (int k = threadIdx.x; k < nv * T; k += kBlock) {
+            const int v = k / T, t = k - v * T;
+            mask[(size_t)v0 * T + k] = t < num[v0 + v] ? 1.0f : 0.0f;
+        }
+    }
+}
+
+// The tail of the learned VFEs (voxel_encoder.py:124-129, 184-189): x *= mask; voxelwise = max over T.
+// out[v, c] = max_t (x[v, t, c] * (t < num[v])); arg[v, c] = the t that won (first one on ties), for the backward.
+__global__ void __launch_bounds__(kBlock) k_masked_max(const float* __restrict__ x, const int* __restrict__ num, int m, int T,
+                                                       int C, float* __restrict__ out, int* __restrict__ arg)
+{
+    const long long k = (long long)blockIdx.x * kBlock + threadIdx.x;
+    if (k >= (long long)m * C) return;
+    const int v = (int)(k / C), c = (int)(k - (long long)v * C);
+    const int n = num[v];
+    const float* xv = x + (size_t)v * T * C + c;
+    float best = __fmul_rn(__ldg(xv), 0 < n ? 1.0f : 0.0f);
+    int bi = 0;
+    for (int t = 1; t < T; ++t) {
+        const float val = __fmul_rn(__ldg(xv + (size_t)t * C), t < n ? 1.0f : 0.0f);
+        if (val > best) { best = val; bi = t; }
+    }
+    out[k] = best;
+    if (arg) arg[k] = bi;
+}
+
+// ---------------------------------------------------------------- index scatter to the BEV plane
+// The camera -> BEV projection of the fusion RPN (second/pytorch/models/rpn.py:957-962):
+//   projected[b, :, dst_y[b, j], dst_x[b, j]] = src[b, :, src0[j], src1[j]]   for j = 0 .. P-1, zeros elsewhere,
+// a Python loop over the batch of advanced-index assignments in the reference (last j wins where several pixels
+// fall into one cell, as on the CPU).  Same gather structure as the voxel scatter: a [B, ny, nx] map of the
+// winning j (atomicMax, so the map is filled with -1 first), then every output element is written exactly once.
+__global__ void __launch_bounds__(kBlock) k_fill_i32(int* __restrict__ p, size_t n, int value)
+{
+    const size_t stride = (size_t)gridDim.x * kBlock;
+    for (size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) p[i] = value;
+}
+
+__global__ void __launch_bounds__(kBlock) k_idx_map(const int2* __restrict__ dst_xy, int b, int np, int ny, int nx,
+                                                    int* __restrict__ map)
+{
+    const long long k = (long long)blockIdx.x * kBlock + threadIdx.x;
+    if (k >= (long long)b * np) return;
+    const int bb = (int)(k / np), j = (int)(k - (long long)bb * np);
+    const int2 q = __ldg(dst_xy + k);
+    if ((unsigned)q.x >= (unsigned)nx || (unsigned)q.y >= (unsigned)ny) return;
+    atomicMax(map + ((size_t)bb * ny + q.y) * nx + q.x, j);
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(kBlock) k_idx_canvas(const float* __restrict__ src, const int2* __restrict__ src_idx,
+                                                       int c, int b, int s0, int s1, int ny, int nx,
+                                                       const int* __restrict__ map, float* __restrict__ out, int ch_per)
+{
+    const int nxg = nx / VEC;
+    const long long g = (long long)blockIdx.x * kBlock + threadIdx.x;
+    if (g >= (long long)b * ny * nxg) return;
+    const int xg = (int)(g % nxg);
+    const long long r = g / nxg;
+    const int y = (int)(r % ny), bb = (int)(r / ny);
+    const size_t cell0 = ((size_t)bb * ny + y) * nx + (size_t)xg * VEC;
+    int off[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const int v = __ldg(map + cell0 + j);
+        off[j] = -1;
+        if (v >= 0) {
+            int2 sp = make_int2(v / s1, v % s1);             // implicit mesh: pixel j = (j / s1, j % s1)
+            if (src_idx) sp = __ldg(src_idx + v);
+            if ((unsigned)sp.x < (unsigned)s0 && (unsigned)sp.y < (unsigned)s1) off[j] = sp.x * s1 + sp.y;
+        }
+    }
+    const int ch0 = blockIdx.y * ch_per, ch1 = min(c, ch0 + ch_per);
+    const size_t splane = (size_t)s0 * s1, oplane = (size_t)ny * nx;
+    const float* sb = src + ((size_t)bb * c + ch0) * splane;
+    float* o = out + ((size_t)bb * c + ch0) * oplane + (size_t)y * nx + (size_t)xg * VEC;
+    for (int ch = ch0; ch < ch1; ++ch, sb += splane, o += oplane) {
+        float val[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) val[j] = off[j] >= 0 ? __ldg(sb + off[j]) : 0.0f;
+        if (VEC == 4) *reinterpret_cast<float4*>(o) = make_float4(val[0], val[1 % VEC], val[2 % VEC], val[3 % VEC]);
+        else o[0] = val[0];
+    }
+}
+
 }  // namespace bvx

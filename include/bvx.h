@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BVX_ABI_VERSION 3
+#define BVX_ABI_VERSION 4
 
 typedef enum bvx_status {
     BVX_OK = 0,
@@ -291,6 +291,39 @@ int bvx_scatter_bev_dev(const float* feats, const int32_t* coors4,
                         const int32_t* m_dev, int32_t m_cap, int32_t c, int32_t b,
                         int32_t d, int32_t ny, int32_t nx, float* canvas,
                         void* stream);
+
+/* The bandwidth part of the learned VFEs VoxelFeatureExtractor / V2
+ * (second/pytorch/models/voxel_encoder.py:68-189; their linear + batch-norm
+ * layers stay torch modules, see modules.py).
+ * bvx_vfe_augment = what their forward does before the first linear layer
+ * (voxel_encoder.py:100-112, 165-176): points_mean = sum_t xyz / num;
+ *   out[v, t, :] = (voxels[v, t, :f], xyz - points_mean [, |xyz|_2])   [m, t, f + 3 (+ 1)]
+ * for all t slots -- the reference does not mask its input, a padded slot gets
+ * -points_mean --, and mask[v, t] = (t < num[v]) as float, the padding indicator
+ * of get_paddings_indicator (voxel_encoder.py:12-33); mask may be NULL.
+ * bvx_masked_max = their tail (voxel_encoder.py:124-129, 184-189): x *= mask,
+ * voxelwise = max over t:  out[v, c] = max_t x[v, t, c] * (t < num[v]);
+ * argmax (optional, [m, c] int32) = the winning t, for a backward pass. */
+int bvx_vfe_augment(const float* voxels, const int32_t* num_points, int32_t m,
+                    int32_t t, int32_t f, int32_t with_distance, float* out,
+                    float* mask, void* stream);
+int bvx_masked_max(const float* x, const int32_t* num_points, int32_t m,
+                   int32_t t, int32_t c, float* out, int32_t* argmax,
+                   void* stream);
+
+/* Camera -> BEV projection scatter of the fusion RPN
+ * (second/pytorch/models/rpn.py:957-962), for the whole batch in one call:
+ *   out[b, :, dst_xy[b, j].y, dst_xy[b, j].x] = src[b, :, src_idx[j].0, src_idx[j].1]
+ * for j = 0 .. np-1, zeros elsewhere; where several j fall into one cell the last
+ * one wins (what the reference's sequential CPU assignment does).
+ *   src      [b, c, s0, s1] f32      out [b, c, ny, nx] f32 (16-byte aligned)
+ *   src_idx  [np, 2] int32 (first, second index into s0 x s1), shared by the batch;
+ *            NULL = the implicit mesh j -> (j / s1, j % s1)
+ *   dst_xy   [b, np, 2] int32 (x, y); out-of-range targets are skipped. */
+int bvx_scatter_index_bev(const float* src, int32_t b, int32_t c, int32_t s0,
+                          int32_t s1, const int32_t* src_idx,
+                          const int32_t* dst_xy, int32_t np, int32_t ny,
+                          int32_t nx, float* out, void* stream);
 
 /* Anchors area from voxel coordinates, the computation
  * behind the reference's anchors_mask:
