@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # BVX_LIB: an experiment build of the same sources (tools/variants.sh); the product is libbvx.so
 LIB_PATH = os.environ.get("BVX_LIB") or os.path.join(_HERE, "libbvx.so")
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 BVX_OK = 0
 BVX_ERR_BAD_ARGUMENT = 1
@@ -96,6 +96,7 @@ SYMBOLS = {
     "bvx_masked_max": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
     "bvx_scatter_index_bev": (ctypes.c_int, [_vp, _i32, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "bvx_scatter_bev": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "bvx_scatter_bev_static": (ctypes.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_scatter_bev_dev": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "bvx_anchors_area_workspace_bytes": (ctypes.c_size_t, [_i32, _i32, _i32, _i32, _i32]),
     "bvx_anchors_area": (ctypes.c_int, [_vp, _i32, _i32, _i32, ctypes.POINTER(ctypes.c_float),

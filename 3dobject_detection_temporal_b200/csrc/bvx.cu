@@ -1659,6 +1659,80 @@ extern "C" int bvx_masked_max(const float* x, const int32_t* num_points, int32_t
     return BVX_OK;
 }
 
+// ---------------------------------------------------------------- BEV scatter without any allocation
+// bvx_scatter_bev keeps its voxel-index map in a cudaMalloc'ed buffer (scatter_map above).  Callers that
+// cannot allocate (code under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) get the
+// same two kernels with the map in a file-scope device array: BVX_STATIC_SCATTER_CELLS ints = 4 MB that every
+// GPU loading the library holds until exit.  In host code the array's NAME is a host-side stand-in, not a
+// device address: the address is looked up once per device, with that device current, and passed to the kernels.
+static __device__ __align__(256) int g_static_scatter_map[BVX_STATIC_SCATTER_CELLS];
+static std::mutex g_static_map_mu;
+static int* g_static_map_ptr[64] = {};
+
+static int static_scatter_map(int** out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_static_map_mu);
+    if (!g_static_map_ptr[dev]) {
+        int* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_static_scatter_map);     // set-up: once per device, that device current
+        if (e != cudaSuccess || !ptr)
+            return fail(nullptr, BVX_ERR_CUDA, "cudaGetSymbolAddress(static scatter map): %s", cudaGetErrorString(e));
+        g_static_map_ptr[dev] = ptr;
+    }
+    *out = g_static_map_ptr[dev];
+    return BVX_OK;
+}
+
+extern "C" int bvx_scatter_bev_static(const float* feats, const int32_t* coors4, int32_t m, int32_t c, int32_t b,
+                                      int32_t d, int32_t ny, int32_t nx, float* canvas, void* stream)
+{
+    if (m < 0 || c < 1 || b < 1 || d < 1 || ny < 1 || nx < 1)
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "bad scatter shape");
+    if (!canvas || (m > 0 && (!feats || !coors4))) return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "null argument");
+    if (((uintptr_t)canvas & 15) || ((uintptr_t)coors4 & 15))
+        return fail(nullptr, BVX_ERR_BAD_ARGUMENT, "canvas/coors must be 16-byte aligned");
+    const unsigned long long cells = (unsigned long long)b * d * ny * nx;
+    if (cells > (unsigned long long)BVX_STATIC_SCATTER_CELLS)
+        return fail(nullptr, BVX_ERR_WORKSPACE,
+                    "bvx_scatter_bev_static: b*d*ny*nx = %llu cells exceed the static map of %d cells "
+                    "(BVX_STATIC_SCATTER_CELLS); use bvx_scatter_bev", cells, (int)BVX_STATIC_SCATTER_CELLS);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (m == 0) {
+        // nothing to place: the canvas is all zeros
+        const size_t total = (size_t)cells * c, n4 = total >> 2;
+        const int fb = (int)std::min<size_t>((n4 + kBlock - 1) / kBlock + 1, 148 * 16);
+        k_fill_zero<<<fb, kBlock, 0, st>>>(reinterpret_cast<float4*>(canvas), n4, canvas + (n4 << 2), (int)(total & 3));
+        g_launches += 1;
+    } else {
+        int* map = nullptr;
+        const int rc = static_scatter_map(&map);
+        if (rc) return rc;
+        // The map keeps the last call's contents and is NOT cleared: k_bev_canvas accepts an entry v only if
+        // v < m and coors4[v] is that very cell, so stale entries are harmless (nothing must start at zero).
+        k_bev_map<<<(m + kBlock - 1) / kBlock, kBlock, 0, st>>>(reinterpret_cast<const int4*>(coors4), m, nullptr, b, d, ny, nx, map);
+        const bool vec = (nx & 3) == 0;
+        const long long groups = (long long)(cells / (vec ? 4 : 1));
+        const int gb = (int)((groups + kBlock - 1) / kBlock);
+        int ch_per = c;
+        while (ch_per > 8 || (ch_per > 1 && (long long)gb * ((c + ch_per - 1) / ch_per) < 148 * 8)) ch_per = (ch_per + 1) / 2;
+        const dim3 grid(gb, (c + ch_per - 1) / ch_per);
+        if (vec)
+            k_bev_canvas<4><<<grid, kBlock, 0, st>>>(feats, reinterpret_cast<const int4*>(coors4), m, nullptr, c, b, d, ny, nx,
+                                                     map, canvas, ch_per);
+        else
+            k_bev_canvas<1><<<grid, kBlock, 0, st>>>(feats, reinterpret_cast<const int4*>(coors4), m, nullptr, c, b, d, ny, nx,
+                                                     map, canvas, ch_per);
+        g_launches += 2;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, BVX_ERR_CUDA, "static scatter launch: %s", cudaGetErrorString(e));
+    return BVX_OK;
+}
+
 // ---------------------------------------------------------------- anchors area
 struct AaLayout {
     AnchorsMap mp;

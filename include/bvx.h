@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BVX_ABI_VERSION 4
+#define BVX_ABI_VERSION 5
 
 typedef enum bvx_status {
     BVX_OK = 0,
@@ -291,6 +291,27 @@ int bvx_scatter_bev_dev(const float* feats, const int32_t* coors4,
                         const int32_t* m_dev, int32_t m_cap, int32_t c, int32_t b,
                         int32_t d, int32_t ny, int32_t nx, float* canvas,
                         void* stream);
+
+/* bvx_scatter_bev for callers that cannot allocate.  NO COUNTERPART IN THE
+ * REFERENCE: added for code under CUDA
+ * graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Same arguments, same result as bvx_scatter_bev, but the voxel-index map the
+ * two kernels use as scratch lives in a file-scope device array of
+ * BVX_STATIC_SCATTER_CELLS int32 (4 MB, held by every GPU that loads the
+ * library until exit) instead of a cudaMalloc'ed buffer: the call allocates and
+ * frees nothing, on the device or through any library.
+ *   limit   b * d * ny * nx <= BVX_STATIC_SCATTER_CELLS, else BVX_ERR_WORKSPACE
+ *           (cfg3's 496 x 432 canvas: up to 4 frames per call).
+ *   sharing every call on a device shares the one array; it keeps the last call's
+ *           contents and is not cleared -- an entry only counts if coors4 of the
+ *           voxel it names is that very cell, so stale entries are harmless.
+ *           Calls that OVERLAP on the GPU (different streams, no ordering between
+ *           them) race on the array: order them, or use bvx_scatter_bev, whose
+ *           map is per stream. */
+#define BVX_STATIC_SCATTER_CELLS (1 << 20)
+int bvx_scatter_bev_static(const float* feats, const int32_t* coors4, int32_t m,
+                           int32_t c, int32_t b, int32_t d, int32_t ny,
+                           int32_t nx, float* canvas, void* stream);
 
 /* The bandwidth part of the learned VFEs VoxelFeatureExtractor / V2
  * (second/pytorch/models/voxel_encoder.py:68-189; their linear + batch-norm

@@ -19,7 +19,7 @@ def test_library_exports_every_declared_symbol(pkg):
     lib = ctypes.CDLL(pkg._lib.LIB_PATH)
     for name in declared:
         assert hasattr(lib, name), name
-    assert pkg._lib.load().bvx_abi_version() == pkg._lib.ABI_VERSION == 4
+    assert pkg._lib.load().bvx_abi_version() == pkg._lib.ABI_VERSION == 5
 
 
 def test_struct_layouts_match_header(pkg):
