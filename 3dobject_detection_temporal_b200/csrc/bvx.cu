@@ -22,6 +22,7 @@
 #include <xmmintrin.h>
 #endif
 #include <sched.h>
+#include <unistd.h>
 #include <chrono>
 #include <condition_variable>
 #include <functional>
@@ -1097,6 +1098,7 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
                                       int32_t* fvo_host, cudaStream_t st)
 {
     const int T = h->cfg.max_num_points;
+    const auto t_entry = std::chrono::steady_clock::now();
     // sub-batches: 8 when the rows come home by DMA; 16 with host assembly, where the first and the last
     // sub-batch are not overlapped with anything (measured cfg4: 4 / 8 / 12 / 16 -> 3.16 / 2.71 / 2.58 / 2.52 ms)
     const int nsub = std::min(b, h->host_assemble ? 16 : 8);
@@ -1323,8 +1325,8 @@ static int generate_batched_pipelined(bvx_handle* h, const float* points, const 
         if (rc) return rc;
     }
     if (trace)
-        fprintf(stderr, "[bvx] leg3 %.0f us: wait kernels %.0f, wait copies %.0f, assemble %.0f (%d threads)\n",
-                us(t_leg3, now()), t_done, t_out, t_asm, h->pool ? h->pool->shares : 0);
+        fprintf(stderr, "[bvx] pid %d mode %d: enqueue %.0f us, leg3 %.0f us: wait kernels %.0f, wait copies %.0f, assemble %.0f (%d threads)\n",
+                (int)getpid(), mode, us(t_entry, t_leg3), us(t_leg3, now()), t_done, t_out, t_asm, h->pool ? h->pool->shares : 0);
     // where the cut-offs were this time: the next call's prefix
     if (brk) {
         float r = 0.f;

@@ -1,24 +1,33 @@
-"""Where the pipelined host form spends its time (BVX_TRACE=1 prints the legs of every call)."""
+"""End-to-end arm of bench.py only (cfg4, pinned numpy in/out), with BVX_TRACE lines per call on stderr and the
+wall time of every call per rank.  usage: [torchrun ...] python tools/e2e_trace.py [steps=10] [host_threads]"""
 import importlib, os, sys, time
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pkg = importlib.import_module("3dobject_detection_temporal_b200")
+steps = int(sys.argv[1]) if len(sys.argv) > 1 else 10
+threads = int(sys.argv[2]) if len(sys.argv) > 2 else None
+rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+torch.cuda.set_device(local)
+if world > 1:
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
 c = pkg.synth.CONFIGS["cfg4"]
-B, T, F, cap = 64, 5, 4, c["max_voxels"]
-frames = [pkg.synth.lidar_frame(c["n"], "kitti", i) for i in range(B)]
-offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.int32)
-host = np.concatenate(frames, axis=0)
-hp = pkg.pinned_empty(host.shape, np.float32); hp[:] = host
-hout = (pkg.pinned_empty((B * cap, T, F), np.float32), pkg.pinned_empty((B * cap, 4), np.int32),
-        pkg.pinned_empty((B * cap,), np.int32), pkg.pinned_empty((B + 1,), np.int32))
-for asm, mod in ((True, 0), (False, 0)):
-    g = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, host_assemble=asm)
-    for _ in range(3):
-        g.generate_batched(hp, offs, out=hout)
-    os.environ["BVX_TRACE"] = "1"
-    t0 = time.perf_counter()
-    for _ in range(3):
-        g.generate_batched(hp, offs, out=hout)
-    print(f"assemble={asm}: {(time.perf_counter() - t0) / 3 * 1e3:.3f} ms/call", flush=True)
-    os.environ.pop("BVX_TRACE")
-    g.close()
+B, T, cap = 64, c["max_num_points"], c["max_voxels"]
+sets = []
+for k in range(3):
+    fr = [pkg.synth.lidar_frame(c["n"], "kitti", 1000 * k + g) for g in pkg.shard_frames(B * world, rank, world)]
+    hp = pkg.pinned_empty((B * c["n"], 4), np.float32); hp[:] = np.concatenate(fr); sets.append(hp)
+offs = (np.arange(B + 1) * c["n"]).astype(np.int32)
+out = (pkg.pinned_empty((B * cap, T, 4), np.float32), pkg.pinned_empty((B * cap, 4), np.int32),
+       pkg.pinned_empty((B * cap,), np.int32), pkg.pinned_empty((B + 1,), np.int32))
+gen = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], T, cap, device=torch.device("cuda", local),
+                         host_threads=threads)
+for i in range(3):
+    gen.generate_batched(sets[i % 3], offs, out=out)
+if world > 1:
+    torch.distributed.barrier()
+ts = []
+for i in range(steps):
+    t0 = time.perf_counter(); gen.generate_batched(sets[i % 3], offs, out=out); ts.append((time.perf_counter() - t0) * 1e3)
+print(f"rank {rank} pid {os.getpid()} threads {gen._host_threads} calls ms: " + " ".join(f"{t:.2f}" for t in ts), flush=True)
+if world > 1:
+    torch.distributed.destroy_process_group()
