@@ -738,8 +738,11 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
-        // one warp per chunk for the numbering, all resident at once (148 SMs x 8 blocks), + 1 publisher per frame
-        const int gx = std::max(1, std::min((chunks + kWarps - 1) / kWarps, std::max(2, 148 * 8 / B - 1)));
+        // one warp per chunk for the numbering; small batches get up to 4x as many blocks, so that the extras (spread
+        // over all warps of a frame) are one round of dependent atomics per warp instead of several; all blocks
+        // resident at once (148 SMs x 8 blocks), + 1 publisher per frame
+        const int n2 = std::max(1, (chunks + kWarps - 1) / kWarps);
+        const int gx = std::max(1, std::min(4 * n2, std::max(2, 148 * 8 / B - 1)));
         const int n2e = 0;
         if (chunks > h->scan_smem_chunks) {
             k_scan_big<<<B, kBlock, 0, st>>>(p);
@@ -752,16 +755,21 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         }
     }
     if (chunks > 0 && T > kChainMaxT) {
-        const int ob = std::min(4096, (h->cfg.max_points + kBlock - 1) / kBlock);
+        const int ob = std::min(148 * 4, (h->cfg.max_points + kBlock - 1) / kBlock);
         ProfScope ps(h, 4, st);
-        k_overflow<<<ob, kBlock, 0, st>>>(p);
-        g_launches += 1;
-        note(cudaGetLastError());
+        note(launch_k(h, k_overflow, dim3(ob), kBlock, 0, st, p));
     }
     if (small) {
         const int tiles = (cap + kBlock - 1) / kBlock;
-        const size_t smem = (size_t)kWarps * 32 * T * 16;
-        const dim3 grid(tiles + rchunks, B);
+        const size_t smem = (size_t)kGatherVpt * kWarps * 32 * T * 16;
+        const dim3 grid((tiles + kGatherVpt - 1) / kGatherVpt + rchunks, B);
+        if (smem > 48 * 1024) {
+            switch (T) {
+#define BVX_GA(TT) case TT: note(cudaFuncSetAttribute(k_gather_small<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); break;
+                BVX_GA(1) BVX_GA(2) BVX_GA(3) BVX_GA(4) BVX_GA(5) BVX_GA(6) BVX_GA(7) BVX_GA(8)
+#undef BVX_GA
+            }
+        }
         ProfScope ps(h, 5, st);
         switch (T) {
 #define BVX_GS(TT) case TT: note(launch_k(h, k_gather_small<TT>, grid, kBlock, smem, st, p, tiles)); break;

@@ -26,6 +26,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef BVX_GATHER_VPT
+#define BVX_GATHER_VPT 1   // measured cfg4: 2 voxels per thread 46.7 us (4 blocks/SM) .. 58.9 (8, spills) against 43.9 for 1
+#endif
+
 namespace bvx {
 
 constexpr unsigned long long kEmpty64 = 0xFFFFFFFFFFFFFFFFull;
@@ -39,12 +43,13 @@ constexpr int kChunkWords = kChunk / 32;
 constexpr int kWarps = kBlock / 32;
 constexpr int kUnit = 32 * kPts;     // 128 points: what one warp owns of a chunk
 constexpr int kScanSmemChunks = 4096;  // frames up to this many chunks are scanned in shared memory by k_mid
+constexpr int kGatherVpt = BVX_GATHER_VPT;   // voxels per thread of the specialised gather
 constexpr int kInlineFrames = 64;      // calls of up to this many frames carry their frame descriptors as kernel arguments
 #ifndef BVX_GATHER_PF
 #define BVX_GATHER_PF 0
 #endif
 #ifndef BVX_GATHER_BLOCKS
-#define BVX_GATHER_BLOCKS 8
+#define BVX_GATHER_BLOCKS 6   // 40 registers; the kernel alone is 1.5 us slower than with 8 blocks of 32, the back-to-back step 6 us faster
 #endif
 #ifndef BVX_INSERT_BLOCKS
 #define BVX_INSERT_BLOCKS 6   // 42 registers, no spills: 59.6 us against 76.4 us with 8 blocks of 32 registers (cfg4 break)
@@ -966,6 +971,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
 // extra is offered here and the bucket keeps the T-1 smallest indices.
 __global__ void __launch_bounds__(kBlock) k_overflow(const __grid_constant__ Pipe p)
 {
+    pdl_prologue();
     const int n = min(((volatile int*)p.counters)[1], p.ovf_cap);
     const int T1 = p.T - 1;
     for (int j = blockIdx.x * kBlock + threadIdx.x; j < n; j += gridDim.x * kBlock) {
@@ -1064,140 +1070,162 @@ __device__ __forceinline__ void cp_async_wait_all()
 }
 
 // Fast path: T <= 8 (extras already sorted by the atomicMin chain), 4 floats per
-// point, 16-byte aligned rows.  One thread per voxel.  The T rows of a voxel are random 16-byte
-// reads: they are copied global -> shared ASYNCHRONOUSLY (cp.async, zero fill for the empty slots),
-// straight to their place in the warp's [32 voxels, T, 4] tile, so no registers are held while they
-// are in flight (24 registers, 8 blocks per SM: what bounds this kernel is the number of such reads
-// in flight); the tile then goes out with fully coalesced 16-byte streaming stores, and the thread
-// reads its own rows back for the coordinates and the fused mean.
-// grid (tiles + reset chunks, B); dynamic smem = kWarps * 32 * T * 16 bytes.
+// point, 16-byte aligned rows.  One thread per voxel, kGatherVpt voxels per thread (tiles of 256 voxels
+// blockIdx.x * kGatherVpt + u): a block is a chain of dependent round trips (indices -> rows -> stores), and
+// what bounds the kernel is how many of the random 16-byte row reads are in flight per SM, so a thread
+// issues the index loads of all its voxels, then the row reads of all of them, before it waits for any.
+// The T rows of a voxel are copied global -> shared ASYNCHRONOUSLY (cp.async, zero fill for the empty slots),
+// straight to their place in the warp's [32 voxels, T, 4] tile, so no registers are held while they are in
+// flight; the tile then goes out with fully coalesced 16-byte streaming stores, and the thread reads its
+// own rows back for the coordinates and the fused mean.
+// grid (ceil(tiles / kGatherVpt) + reset chunks, B); dynamic smem = kGatherVpt * kWarps * 32 * T * 16 bytes.
 template <int T>
 __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(const __grid_constant__ Pipe p, int tiles)
 {
     extern __shared__ float4 smem_v[];
+    constexpr int V = kGatherVpt;
+    constexpr int TX = T > 1 ? T - 1 : 1;
     pdl_prologue();
     const int f = blockIdx.y;
     const FrameDesc fr = frame_desc(p, f);
-    if ((int)blockIdx.x >= tiles) { tidy_frame(p, fr, f); reset_chunk(p, fr, blockIdx.x - tiles); return; }
-    const int v0 = blockIdx.x * kBlock;
+    const int nblk = (tiles + V - 1) / V;
+    if ((int)blockIdx.x >= nblk) { tidy_frame(p, fr, f); reset_chunk(p, fr, blockIdx.x - nblk); return; }
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int v = v0 + threadIdx.x;
-    // The point indices of the voxel are fetched BEFORE the frame's voxel count is known (their addresses
-    // do not depend on it; rows behind the count hold nothing that is used): the block's chain of
-    // dependent round trips is indices -> rows -> stores, not count -> indices -> rows -> stores.
-    int raw0 = kEmptyIdx;
-    int rawx[T > 1 ? T - 1 : 1];
-    int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
-    if (v < p.cap) {
-        raw0 = __ldcs(p.vfirst + (size_t)f * p.cap + v);
-        if (T == 5) {
-            const int4 e = *reinterpret_cast<const int4*>(gb);
-            rawx[0] = e.x; rawx[1 % (T > 1 ? T - 1 : 1)] = e.y; rawx[2 % (T > 1 ? T - 1 : 1)] = e.z; rawx[3 % (T > 1 ? T - 1 : 1)] = e.w;
-        } else {
+    const int tile0 = blockIdx.x * V;
+    // The point indices of the voxels are fetched BEFORE the frame's voxel count is known (their addresses
+    // do not depend on it; rows behind the count hold nothing that is used).
+    int raw0[V];
+    int rawx[V][TX];
 #pragma unroll
-            for (int s = 1; s < T; ++s) rawx[s - 1] = gb[s - 1];
+    for (int u = 0; u < V; ++u) {
+        const int v = (tile0 + u) * kBlock + threadIdx.x;
+        raw0[u] = kEmptyIdx;
+#pragma unroll
+        for (int s = 0; s < TX; ++s) rawx[u][s] = kEmptyIdx;
+        if (v < p.cap) {
+            raw0[u] = __ldcs(p.vfirst + (size_t)f * p.cap + v);
+            const int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
+            if (T == 5) {
+                const int4 e = *reinterpret_cast<const int4*>(gb);
+                rawx[u][0] = e.x; rawx[u][1 % TX] = e.y; rawx[u][2 % TX] = e.z; rawx[u][3 % TX] = e.w;
+            } else {
+#pragma unroll
+                for (int s = 1; s < T; ++s) rawx[u][s - 1] = gb[s - 1];
+            }
         }
-    } else {
-#pragma unroll
-        for (int s = 1; s < T; ++s) rawx[s - 1] = kEmptyIdx;
     }
     const int mf = p.state[f].m;
     const int istar = p.state[f].istar;
     const size_t gbase = (size_t)p.frame_voxel_offsets[f];
-    if (v0 >= mf) { tidy_frame(p, fr, f); return; }
-    const bool live = v < mf;
-    int idx[T];
-    idx[0] = live ? raw0 : kEmptyIdx;
-    if (T > 1) {
-        // the voxel's other points, ascending; a row that held any is put back to empty for the next
-        // call.  Break mode: entries behind the cut-off i* (a suffix of the row) are dropped here.
-        if (T == 5) {
-            if (live && rawx[0] != kEmptyIdx)
-                *reinterpret_cast<int4*>(gb) = make_int4(kEmptyIdx, kEmptyIdx, kEmptyIdx, kEmptyIdx);
-        }
-#pragma unroll
-        for (int s = 1; s < T; ++s) {
-            const int raw = live ? rawx[s - 1] : kEmptyIdx;
-            if (T != 5 && raw != kEmptyIdx) gb[s - 1] = kEmptyIdx;
-            idx[s] = raw < istar ? raw : kEmptyIdx;
-        }
-    }
+    if (tile0 * kBlock >= mf) { tidy_frame(p, fr, f); return; }
     const float4* rows = reinterpret_cast<const float4*>(plain_rows(p, fr));
-    // voxel-major float4 index lane*T + s inside the warp's tile (even T: xor swizzle against bank conflicts)
-    float4* sw = smem_v + wid * (32 * T);
-    int nvalid = 0;
+    int nvalid[V];
+    int keep[V][TX];                  // the voxel's other points in front of the break cut-off (for idx_out)
 #pragma unroll
-    for (int s = 0; s < T; ++s) {
-        int q = lane * T + s;
-        if ((T & 1) == 0) q ^= (q >> 3) & 7;
-        const bool on = idx[s] != kEmptyIdx;
-        cp_async16(sw + q, rows + (on ? idx[s] : 0), on ? 16 : 0);
-        nvalid += on;
+    for (int u = 0; u < V; ++u) {
+        const int v = (tile0 + u) * kBlock + threadIdx.x;
+        const bool live = v < mf;
+        // voxel-major float4 index lane*T + s inside the warp's tile (even T: xor swizzle against bank conflicts)
+        float4* sw = smem_v + (u * kWarps + wid) * (32 * T);
+        int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
+        // a bucket row that held any entry is put back to empty for the next call; entries behind the
+        // break cut-off i* (a suffix of the row) are dropped
+        if (T == 5 && live && rawx[u][0] != kEmptyIdx)
+            *reinterpret_cast<int4*>(gb) = make_int4(kEmptyIdx, kEmptyIdx, kEmptyIdx, kEmptyIdx);
+        int nv = 0;
+#pragma unroll
+        for (int s = 0; s < T; ++s) {
+            int id;
+            if (s == 0) {
+                id = live ? raw0[u] : kEmptyIdx;
+            } else {
+                const int raw = live ? rawx[u][s - 1] : kEmptyIdx;
+                if (T != 5 && raw != kEmptyIdx) gb[s - 1] = kEmptyIdx;
+                id = raw < istar ? raw : kEmptyIdx;
+                keep[u][s - 1] = id;
+            }
+            int q = lane * T + s;
+            if ((T & 1) == 0) q ^= (q >> 3) & 7;
+            const bool on = id != kEmptyIdx;
+            cp_async16(sw + q, rows + (on ? id : 0), on ? 16 : 0);
+            nv += on;
+        }
+        nvalid[u] = nv;
     }
     cp_async_wait_all();
     __syncwarp();
-    if (p.voxels) {
-        const int wv0 = v0 + wid * 32;                    // first voxel of this warp
-        const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
-        float4* out = reinterpret_cast<float4*>(p.voxels) + (gbase + wv0) * T;
 #pragma unroll
-        for (int s = 0; s < T; ++s) {
-            const int j = s * 32 + lane;
-            int q = j;
+    for (int u = 0; u < V; ++u) {
+        const int v0 = (tile0 + u) * kBlock;
+        if (v0 >= mf) break;                               // (block-uniform)
+        const int v = v0 + threadIdx.x;
+        const bool live = v < mf;
+        float4* sw = smem_v + (u * kWarps + wid) * (32 * T);
+        if (p.voxels) {
+            const int wv0 = v0 + wid * 32;                    // first voxel of this warp
+            const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
+            float4* out = reinterpret_cast<float4*>(p.voxels) + (gbase + wv0) * T;
+#pragma unroll
+            for (int s = 0; s < T; ++s) {
+                const int j = s * 32 + lane;
+                int q = j;
+                if ((T & 1) == 0) q ^= (q >> 3) & 7;
+                if (j < wn * T) __stcs(out + j, sw[q]);
+            }
+        }
+        auto own = [&](int slot) {                            // this voxel's rows, back from the tile
+            int q = lane * T + slot;
             if ((T & 1) == 0) q ^= (q >> 3) & 7;
-            if (j < wn * T) __stcs(out + j, sw[q]);
-        }
-    }
-    auto own = [&](int slot) {                            // this voxel's rows, back from the tile
-        int q = lane * T + slot;
-        if ((T & 1) == 0) q ^= (q >> 3) & 7;
-        return sw[q];
-    };
-    if (p.crow) {
-        // compact rows for the host form: the tile reserves a range for its kept points, each voxel
-        // writes its rows (slots 0 .. nvalid-1) at its prefix inside the range
-        __shared__ int s_scan[kWarps + 1];
-        __shared__ int s_base;
-        int tot;
-        const int ex = block_exclusive_scan(nvalid, &tot, s_scan);
-        if (threadIdx.x == 0) {
-            s_base = atomicAdd(&p.counters[2], tot);
-            p.tile_base[f * tiles + blockIdx.x] = s_base;
-            atomicAdd(&p.state[f].rows, tot);
-        }
-        __syncthreads();
-        float4* dst = p.crow + s_base + ex;
+            return sw[q];
+        };
+        if (p.crow) {
+            // compact rows for the host form: the tile reserves a range for its kept points, each voxel
+            // writes its rows (slots 0 .. nvalid-1) at its prefix inside the range
+            __shared__ int s_scan[kWarps + 1];
+            __shared__ int s_base;
+            int tot;
+            const int ex = block_exclusive_scan(nvalid[u], &tot, s_scan);
+            if (threadIdx.x == 0) {
+                s_base = atomicAdd(&p.counters[2], tot);
+                p.tile_base[f * tiles + tile0 + u] = s_base;
+                atomicAdd(&p.state[f].rows, tot);
+            }
+            __syncthreads();
+            float4* dst = p.crow + s_base + ex;
 #pragma unroll
-        for (int s = 0; s < T; ++s)
-            if (s < nvalid) __stcs(dst + s, own(s));
+            for (int s = 0; s < T; ++s)
+                if (s < nvalid[u]) __stcs(dst + s, own(s));
+            __syncthreads();                                  // s_base is rewritten by the next tile
+        }
+        if (!live) continue;
+        const size_t gv = gbase + v;
+        if (p.idx_out) {
+            p.idx_out[gv * T] = raw0[u];
+#pragma unroll
+            for (int s = 1; s < T; ++s) p.idx_out[gv * T + s] = keep[u][s - 1] == kEmptyIdx ? -1 : keep[u][s - 1];
+        }
+        p.num_points[gv] = nvalid[u];
+        const float4 r0 = own(0);
+        write_coor(p, f, gv, cell_of(p.g, r0.x, r0.y, r0.z));
+        if (p.mean_out) {
+            // sum over the T slots in slot order (zeros included), like the reference's features.sum(dim=1)
+            float sx = __fadd_rn(0.f, r0.x), sy = __fadd_rn(0.f, r0.y), sz = __fadd_rn(0.f, r0.z), swt = __fadd_rn(0.f, r0.w);
+#pragma unroll
+            for (int s = 1; s < T; ++s) {
+                const float4 r = own(s);
+                sx = __fadd_rn(sx, r.x); sy = __fadd_rn(sy, r.y);
+                sz = __fadd_rn(sz, r.z); swt = __fadd_rn(swt, r.w);
+            }
+            const float nf = (float)nvalid[u];
+            const float m4[4] = {__fdiv_rn(sx, nf), __fdiv_rn(sy, nf), __fdiv_rn(sz, nf), __fdiv_rn(swt, nf)};
+            if (p.mean_c == 4) {
+                reinterpret_cast<float4*>(p.mean_out)[gv] = make_float4(m4[0], m4[1], m4[2], m4[3]);
+            } else {
+                for (int c = 0; c < p.mean_c; ++c) p.mean_out[gv * p.mean_c + c] = m4[c];
+            }
+        }
     }
     tidy_frame(p, fr, f);        // last: nothing of this block waits for it
-    if (!live) return;
-    const size_t gv = gbase + v;
-    if (p.idx_out) {
-#pragma unroll
-        for (int s = 0; s < T; ++s) p.idx_out[gv * T + s] = idx[s] == kEmptyIdx ? -1 : idx[s];
-    }
-    p.num_points[gv] = nvalid;
-    const float4 r0 = own(0);
-    write_coor(p, f, gv, cell_of(p.g, r0.x, r0.y, r0.z));
-    if (p.mean_out) {
-        // sum over the T slots in slot order (zeros included), like the reference's features.sum(dim=1)
-        float sx = __fadd_rn(0.f, r0.x), sy = __fadd_rn(0.f, r0.y), sz = __fadd_rn(0.f, r0.z), swt = __fadd_rn(0.f, r0.w);
-#pragma unroll
-        for (int s = 1; s < T; ++s) {
-            const float4 r = own(s);
-            sx = __fadd_rn(sx, r.x); sy = __fadd_rn(sy, r.y);
-            sz = __fadd_rn(sz, r.z); swt = __fadd_rn(swt, r.w);
-        }
-        const float nf = (float)nvalid;
-        const float m4[4] = {__fdiv_rn(sx, nf), __fdiv_rn(sy, nf), __fdiv_rn(sz, nf), __fdiv_rn(swt, nf)};
-        if (p.mean_c == 4) {
-            reinterpret_cast<float4*>(p.mean_out)[gv] = make_float4(m4[0], m4[1], m4[2], m4[3]);
-        } else {
-            for (int c = 0; c < p.mean_c; ++c) p.mean_out[gv * p.mean_c + c] = m4[c];
-        }
-    }
 }
 
 // General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T entries: the first
