@@ -723,6 +723,22 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         const unsigned long long tbytes = (1ull << h->max_tbl_lg) * 8;
         p.clear_rows = (int)std::max<unsigned long long>(1, std::min<unsigned long long>(256, tbytes / (64 * 1024)));
     }
+    int tail = 0;
+    if (hashed && chunks > 0 && B <= 8 && !getenv("BVX_NO_TAIL_CLEAR")) {
+        // small batches: the gather empties the tables for the next call (64 KB slices); signature = FNV-1a over the regions
+        tail = p.clear_rows;
+        unsigned long long sg = 1469598103934665603ull;
+        auto mix = [&](unsigned long long v) { for (int k = 0; k < 8; ++k) { sg ^= (v >> (8 * k)) & 0xFF; sg *= 1099511628211ull; } };
+        mix((unsigned long long)B);
+        for (int f = 0; f < B; ++f) { mix(h->h_frames[f].tbl_off); mix(h->h_frames[f].tbl_mask); mix((unsigned long long)(h->h_frames[f].n > 0)); }
+        if ((unsigned int)sg == 0 && (unsigned int)(sg >> 32) == 0) sg = 1;
+        p.tail_clear = tail;
+        p.tail_sig[0] = (unsigned int)sg;
+        p.tail_sig[1] = (unsigned int)(sg >> 32);
+    } else {
+        p.tail_sig[0] = 0xFFFFFFFFu; p.tail_sig[1] = 0xFFFFFFFFu;      // never stored: counters[4..5] hold 0 after such a call
+    }
+    const int extra = hashed ? tail : rchunks;           // trailing blocks of the gather (table reset / clear)
     cudaError_t le = cudaSuccess;
     auto note = [&](cudaError_t e) { if (le == cudaSuccess) le = e; };
     if (chunks > 0) {
@@ -762,7 +778,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     if (small) {
         const int tiles = (cap + kBlock - 1) / kBlock;
         const size_t smem = (size_t)kGatherVpt * kWarps * 32 * T * 16;
-        const dim3 grid((tiles + kGatherVpt - 1) / kGatherVpt + rchunks, B);
+        const dim3 grid((tiles + kGatherVpt - 1) / kGatherVpt + extra, B);
         if (smem > 48 * 1024) {
             switch (T) {
 #define BVX_GA(TT) case TT: note(cudaFuncSetAttribute(k_gather_small<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); break;
@@ -781,7 +797,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         if (gather_smem > 48 * 1024)
             note(cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gather_smem));
         ProfScope ps(h, 5, st);
-        note(launch_k(h, k_gather, dim3(tiles + rchunks, B), kBlock, gather_smem, st, p, tiles, gather_vt));
+        note(launch_k(h, k_gather, dim3(tiles + extra, B), kBlock, gather_smem, st, p, tiles, gather_vt));
     }
     if (le != cudaSuccess) return fail(h, BVX_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(le));
     CK(h, cudaGetLastError());

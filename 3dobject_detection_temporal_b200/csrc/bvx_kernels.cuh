@@ -140,6 +140,10 @@ struct Pipe {
     int frame_base;      // batch index of frame 0 of this call (sub-batches of a pipelined host call)
     int ovf_cap;
     int vec4;            // f_in == 4 and every segment pointer 16-byte aligned
+    int tail_clear;      // hashed tables, small batches: the gather's trailing blocks empty the tables for the NEXT call in
+                         // this many slices per frame and leave tail_sig in counters[4..5]; a call that finds its own
+                         // signature there (same table regions, nothing ran in between) skips the clear and its handshake
+    unsigned int tail_sig[2];   // 64-bit signature of the call's table regions (never 0)
     int clear_rows;      // hashed tables: slices each table is cleared in = leading block rows of k_insert (0: dense grid)
     // outputs
     float4* crow;        // optional, specialised gather only: the kept rows of the call, compact (no padding): a tile
@@ -339,10 +343,10 @@ __device__ __forceinline__ void fetch_row(const Pipe& p, const FrameDesc& fr, in
 // the points that are not the first of their voxel, and only they need a pass of their own.
 // (Recording the first point as seen instead of the slot saves k_mid the table access only for
 // warps in which no lane's record went stale -- one warp in ten: measured slower.)
-__device__ __forceinline__ void clear_slice(const Pipe& p, const FrameDesc& fr, int s)
+__device__ __forceinline__ void clear_slice(const Pipe& p, const FrameDesc& fr, int s, int nslices)
 {
     const unsigned int n2 = (fr.tbl_mask + 1u) >> 1;        // uint4 = two slots
-    const unsigned int per = (n2 + p.clear_rows - 1) / p.clear_rows;
+    const unsigned int per = (n2 + nslices - 1) / nslices;
     const unsigned int lo = min(n2, (unsigned)s * per), hi = min(n2, lo + per);
     uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
     const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
@@ -357,7 +361,10 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
     const int f = blockIdx.x;
     const FrameDesc fr = frame_desc(p, f);
     FrameState* st = p.state + f;
+    // tables already emptied by the previous call's gather (same table regions: its signature is still there)?
+    const bool pre = __ldcg(p.counters + 4) == (int)p.tail_sig[0] && __ldcg(p.counters + 5) == (int)p.tail_sig[1];
     if ((int)blockIdx.y < p.clear_rows) {
+        if (pre) return;
         // Clear rows: the frame's table is emptied here, right before it is used, with normal
         // stores -- whole sectors, so the lines are allocated in the L2 without a DRAM fill and
         // the atomics below find them there.  Slices are CLAIMED (not owned by block index): an
@@ -367,7 +374,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
             if (threadIdx.x == 0) s_slice = atomicAdd(&st->clear_claim, 1);
             __syncthreads();
             if (s_slice < p.clear_rows) {
-                clear_slice(p, fr, s_slice);
+                clear_slice(p, fr, s_slice, p.clear_rows);
                 __threadfence();
                 __syncthreads();
                 if (threadIdx.x == 0) atomicAdd(&st->cleared, 1);
@@ -383,7 +390,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
     // ticket -> (chunk, table-ready flag); a chunk past the break cut-off is skipped
     auto take = [&](unsigned long long t, int q) {
         int c = (int)((unsigned int)t & 0x7FFFFFFFu);
-        s_rdy[q] = (int)(((unsigned int)t >> 31) | (p.clear_rows == 0));   // bit 31: the table is known to be empty
+        s_rdy[q] = (int)(((unsigned int)t >> 31) | (p.clear_rows == 0) | pre);   // bit 31: the table is known to be empty
         if (brk && (int)(t >> 32) > p.cap && (long long)c * kChunk < fr.n) {
             atomicMin(&st->n_eff, c * kChunk);
             c = 0x7FFFFFF;                             // skipped
@@ -445,7 +452,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
                 if (threadIdx.x == 0) s_slice = atomicAdd(&st->clear_claim, 1);
                 __syncthreads();
                 if (s_slice >= p.clear_rows) break;
-                clear_slice(p, fr, s_slice);
+                clear_slice(p, fr, s_slice, p.clear_rows);
                 __threadfence();
                 __syncthreads();
                 if (threadIdx.x == 0) atomicAdd(&st->cleared, 1);
@@ -1013,6 +1020,14 @@ __device__ __forceinline__ void reset_chunk(const Pipe& p, const FrameDesc& fr, 
     }
 }
 
+// Trailing blocks of both gathers: dense grid -> reset the entries the frame created; hashed grid with tail_clear ->
+// empty one slice of the frame's table for the next call (nothing reads the table any more: k_mid is complete).
+__device__ __forceinline__ void tail_block(const Pipe& p, const FrameDesc& fr, int idx)
+{
+    if (fr.tbl_shift < 0) reset_chunk(p, fr, idx);
+    else if (idx < p.tail_clear && fr.n > 0) clear_slice(p, fr, idx, p.tail_clear);
+}
+
 // Every gather block first does its share of putting the frame's per-call structures back into
 // their between-calls state (the gather is the call's last kernel): displaced-candidate bits and
 // chunk counters to zero, k_insert's per-frame counters to their start values.
@@ -1032,7 +1047,11 @@ __device__ __forceinline__ void tidy_frame(const Pipe& p, const FrameDesc& fr, i
         st->cleared = 0;
         st->clear_claim = 0;
         st->n_eff = 0x7FFFFFFF;
-        if (f == 0) p.counters[1] = 0;
+        if (f == 0) {
+            p.counters[1] = 0;
+            p.counters[4] = p.tail_clear ? (int)p.tail_sig[0] : 0;     // what the tables look like after this call
+            p.counters[5] = p.tail_clear ? (int)p.tail_sig[1] : 0;
+        }
     }
 }
 
@@ -1089,7 +1108,7 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
     const int f = blockIdx.y;
     const FrameDesc fr = frame_desc(p, f);
     const int nblk = (tiles + V - 1) / V;
-    if ((int)blockIdx.x >= nblk) { tidy_frame(p, fr, f); reset_chunk(p, fr, blockIdx.x - nblk); return; }
+    if ((int)blockIdx.x >= nblk) { tidy_frame(p, fr, f); tail_block(p, fr, blockIdx.x - nblk); return; }
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int tile0 = blockIdx.x * V;
     // The point indices of the voxels are fetched BEFORE the frame's voxel count is known (their addresses
@@ -1239,7 +1258,7 @@ __global__ void __launch_bounds__(kBlock) k_gather(const __grid_constant__ Pipe 
     const int f = blockIdx.y;
     const FrameDesc fr = frame_desc(p, f);
     tidy_frame(p, fr, f);
-    if ((int)blockIdx.x >= tiles) { reset_chunk(p, fr, blockIdx.x - tiles); return; }
+    if ((int)blockIdx.x >= tiles) { tail_block(p, fr, blockIdx.x - tiles); return; }
     const int mf = p.state[f].m;
     const int v0 = blockIdx.x * vt;
     if (v0 >= mf) return;

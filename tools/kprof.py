@@ -13,7 +13,7 @@ offs = np.concatenate([[0], np.cumsum([f.shape[0] for f in frames])]).astype(np.
 sets = [torch.from_numpy(np.concatenate([frames[(i + 7 * k) % frames_n] for i in range(frames_n)])).cuda()
         for k in range(3)]
 gen = pkg.VoxelGenerator(c["voxel_size"], c["point_cloud_range"], c["max_num_points"], c["max_voxels"],
-                         overflow=overflow)
+                         overflow=overflow, grid=os.environ.get("BVX_GRID", "hashed"))
 out = gen.generate_batched(sets[0], offs, mean_channels=4, padded=True)
 for i in range(5):
     gen.generate_batched(sets[i % 3], offs, mean_channels=4, padded=True, out=out)
