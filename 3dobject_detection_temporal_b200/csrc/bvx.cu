@@ -392,7 +392,7 @@ extern "C" int bvx_create(const bvx_config* cfg, bvx_handle** out)
     if ((e = dalloc(h, &h->chunkstat, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkstat");
     if ((e = cudaMemset(h->chunkstat, 0, (size_t)h->chunks_cap * 4)) != cudaSuccess) return bail(e, "memset chunkstat");
     if ((e = dalloc(h, &h->extras, (size_t)h->chunks_cap * kChunk)) != cudaSuccess) return bail(e, "alloc extras");
-    if ((e = dalloc(h, &h->extn, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc extn");
+    if ((e = dalloc(h, &h->extn, (size_t)h->chunks_cap * kParts)) != cudaSuccess) return bail(e, "alloc extn");
     if ((e = dalloc(h, &h->chunkbase, (size_t)h->chunks_cap)) != cudaSuccess) return bail(e, "alloc chunkbase");
     if ((e = dalloc(h, &h->vfirst, (size_t)h->voxel_cap)) != cudaSuccess) return bail(e, "alloc vfirst");
     if ((e = dalloc(h, &h->bucket, (size_t)h->voxel_cap * t1)) != cudaSuccess) return bail(e, "alloc bucket");
@@ -449,7 +449,7 @@ struct FrameSpec {
 };
 
 // Chunk rows of k_insert = blocks of one frame in flight at a time (persistent; see run_pipeline).
-static int insert_rows_bound(int B) { return std::max(1, (148 * BVX_INSERT_BLOCKS + B - 1) / B); }
+static int insert_rows_bound(int B) { return std::max(1, (148 * BVX_INSERT_BLOCKS * kParts + B - 1) / B); }
 
 static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
                          int* max_n_out, bool* all_aligned)
@@ -668,8 +668,8 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     if (!small && gather_smem > 200 * 1024)
         return fail(h, BVX_ERR_BAD_ARGUMENT, "max_num_points * features too large for the gather tile (%zu B)", gather_smem);
     const int chunks = (max_n + kChunk - 1) / kChunk;   // chunks of the largest frame
-    if (chunks > 65535 - 256)
-        return fail(h, BVX_ERR_BAD_ARGUMENT, "at most 67M points per frame");
+    if (chunks > (65535 - 256) / kParts)
+        return fail(h, BVX_ERR_BAD_ARGUMENT, "at most %d M points per frame", 67 / kParts);
 
     Pipe p;
     memset(&p, 0, sizeof p);
@@ -747,10 +747,11 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         for (const FrameSpec& fs : frames) crop |= fs.crop && fs.crop->n_planes > 0;
         // persistent chunk rows: about as many blocks as the GPU holds at once (148 SMs x 8), never
         // more rows than the largest frame has chunks
-        const int rows = std::min(chunks, insert_rows_bound(B));
+        const int tickets = (max_n + kTicket - 1) / kTicket;
+        const int rows = std::min(tickets, insert_rows_bound(B));
         const dim3 grid(B, p.clear_rows + rows);
-        if (crop) note(launch_k(h, k_insert<true>, grid, kBlock, 0, st, p));
-        else note(launch_k(h, k_insert<false>, grid, kBlock, 0, st, p));
+        if (crop) note(launch_k(h, k_insert<true>, grid, kIThreads, 0, st, p));
+        else note(launch_k(h, k_insert<false>, grid, kIThreads, 0, st, p));
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);
@@ -767,7 +768,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
             note(launch_k(h, k_mid<true>, dim3(gx + 1, B), kBlock, 16 + (size_t)kWarps * kChunk * 2, st, p, 0, n2e));
         } else {
             const int sc = (std::max(chunks, 1) + 3) & ~3;
-            note(launch_k(h, k_mid<false>, dim3(gx + 1, B), kBlock, (((size_t)sc * 10 + 8 + 15) & ~(size_t)15) + (size_t)kWarps * kChunk * 2, st, p, sc, n2e));
+            note(launch_k(h, k_mid<false>, dim3(gx + 1, B), kBlock, (((size_t)sc * (6 + 4 * kParts) + 8 + 15) & ~(size_t)15) + (size_t)kWarps * kChunk * 2, st, p, sc, n2e));
         }
     }
     if (chunks > 0 && T > kChainMaxT) {

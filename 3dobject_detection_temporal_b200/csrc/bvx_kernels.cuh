@@ -26,6 +26,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef BVX_TICKET
+#define BVX_TICKET 512     // points per k_insert ticket (block iteration): 1024 or 512
+#endif
 #ifndef BVX_GATHER_VPT
 #define BVX_GATHER_VPT 1   // measured cfg4: 2 voxels per thread 46.7 us (4 blocks/SM) .. 58.9 (8, spills) against 43.9 for 1
 #endif
@@ -42,7 +45,10 @@ constexpr int kChunk = kBlock * kPts;  // 1024 points per chunk
 constexpr int kChunkWords = kChunk / 32;
 constexpr int kWarps = kBlock / 32;
 constexpr int kUnit = 32 * kPts;     // 128 points: what one warp owns of a chunk
-constexpr int kScanSmemChunks = 4096;  // frames up to this many chunks are scanned in shared memory by k_mid
+constexpr int kTicket = BVX_TICKET;     // points a k_insert block takes per ticket: a part of a chunk
+constexpr int kParts = kChunk / kTicket;  // parts per chunk; each has its own extras list
+constexpr int kIThreads = kTicket / kPts, kIWarps = kIThreads / 32;
+constexpr int kScanSmemChunks = 2048;  // frames up to this many chunks are scanned in shared memory by k_mid
 constexpr int kGatherVpt = BVX_GATHER_VPT;   // voxels per thread of the specialised gather
 constexpr int kInlineFrames = 64;      // calls of up to this many frames carry their frame descriptors as kernel arguments
 #ifndef BVX_GATHER_PF
@@ -350,11 +356,11 @@ __device__ __forceinline__ void clear_slice(const Pipe& p, const FrameDesc& fr, 
     const unsigned int lo = min(n2, (unsigned)s * per), hi = min(n2, lo + per);
     uint4* t4 = reinterpret_cast<uint4*>(p.table + fr.tbl_off);
     const uint4 e = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-    for (unsigned int j = lo + threadIdx.x; j < hi; j += kBlock) t4[j] = e;
+    for (unsigned int j = lo + threadIdx.x; j < hi; j += blockDim.x) t4[j] = e;
 }
 
 template <bool CROP>
-__global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert(const __grid_constant__ Pipe p)
+__global__ void __launch_bounds__(kIThreads, (CROP ? 4 : BVX_INSERT_BLOCKS) * kParts) k_insert(const __grid_constant__ Pipe p)
 {
     __shared__ int s_tk[2], s_rdy[2], s_extn[2], s_slice;
     pdl_prologue();
@@ -382,7 +388,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
         }
         return;
     }
-    if ((int)(blockIdx.y - p.clear_rows) * kChunk >= fr.n) return;
+    if ((long long)(blockIdx.y - p.clear_rows) * kTicket >= fr.n) return;
     const bool brk = !p.overflow_continue;
     unsigned long long* tbl = p.table + fr.tbl_off;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -391,8 +397,8 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
     auto take = [&](unsigned long long t, int q) {
         int c = (int)((unsigned int)t & 0x7FFFFFFFu);
         s_rdy[q] = (int)(((unsigned int)t >> 31) | (p.clear_rows == 0) | pre);   // bit 31: the table is known to be empty
-        if (brk && (int)(t >> 32) > p.cap && (long long)c * kChunk < fr.n) {
-            atomicMin(&st->n_eff, c * kChunk);
+        if (brk && (int)(t >> 32) > p.cap && (long long)c * kTicket < fr.n) {
+            atomicMin(&st->n_eff, c * kTicket);
             c = 0x7FFFFFF;                             // skipped
         }
         s_tk[q] = c;
@@ -406,7 +412,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
     // exhausted or cut, so the launch carries (rows x frames) blocks, not one block per chunk.
   for (int it = 0;; ++it) {
     const int q = it & 1;
-    const long long basel = (long long)s_tk[q] * kChunk;
+    const long long basel = (long long)s_tk[q] * kTicket;
     const int ready = s_rdy[q];
     if (basel >= fr.n) return;
     const int base = (int)basel;
@@ -475,7 +481,9 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
             active |= 1u << k;
         }
     }
-    int2* ext = p.extras + (size_t)(fr.chunk_off + (base >> 10)) * kChunk;
+    const int part = (base & (kChunk - 1)) / kTicket;           // which part of its chunk this ticket is
+    const size_t lidx = (size_t)(fr.chunk_off + (base >> 10)) * kParts + part;     // its extras list
+    int2* ext = p.extras + lidx * kTicket;       // (every point of the ticket adds at most one entry: itself, or the point it displaced)
     // A displaced point o (it was its cell's first point until point i arrived) becomes an extra of the
     // cell; its chunk counts one first point less and one displaced candidate more.
     auto displaced = [&](unsigned int o, unsigned int slot) {
@@ -567,7 +575,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
                 for (int k = 0; k < kPts; ++k)
                     if (w0 + k < fr.nwords) p.cand[fr.word_off + w0 + k] = cw[k];
             }
-            p.unit8[(size_t)cidx * 16 + wid] = (unsigned char)ncand;
+            p.unit8[(size_t)cidx * 16 + part * kIWarps + wid] = (unsigned char)ncand;
             if (ncand) atomicAdd(p.chunkstat + cidx, (unsigned)ncand);
         }
         if (next) {
@@ -586,7 +594,7 @@ __global__ void __launch_bounds__(kBlock, CROP ? 4 : BVX_INSERT_BLOCKS) k_insert
     if (threadIdx.x == 0) take(tnext, q ^ 1);
     __syncthreads();
     if (threadIdx.x == 0) {
-        p.extn[fr.chunk_off + (base >> 10)] = s_extn[q];
+        p.extn[lidx] = s_extn[q];
         s_extn[q] = 0;                  // next used two iterations from now, behind the next barrier
     }
   }
@@ -808,7 +816,7 @@ __device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, in
     if ((unsigned)r1 < (unsigned)p.cap) place_extra(p, f, r1, e1.x, o1, chain);
 }
 
-// grid (gx + 1, B); dynamic smem: (max chunks per frame + 1) x 10 bytes (not BIG) + 16 KB.  Every block of
+// grid (gx + 1, B); dynamic smem: (max chunks per frame + 1) x (6 + 4 kParts) bytes (not BIG) + 16 KB.  Every block of
 // frame f scans the frame's chunk counts in shared memory (<= 4096 ints: cheaper than a kernel boundary
 // and a last-block chain).  Then the blocks of a frame split by role, so that the three latency chains
 // run side by side instead of one after the other:
@@ -830,8 +838,8 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
     const FrameDesc fr = frame_desc(p, f);
     FrameState* st = p.state + f;
     int* s_pre = s_dyn;                                  // [smem_chunks] exclusive prefix of the first-point counts
-    int* s_epre = s_dyn + smem_chunks;                   // [smem_chunks + 1] exclusive prefix of the extras counts
-    unsigned short* s_lost = reinterpret_cast<unsigned short*>(s_dyn + 2 * smem_chunks + 1);
+    int* s_epre = s_dyn + smem_chunks;                   // [kParts * smem_chunks + 1] exclusive prefix of the extras lists' lengths
+    unsigned short* s_lost = reinterpret_cast<unsigned short*>(s_dyn + (1 + kParts) * smem_chunks + 1);
     unsigned short* s_stage = s_lost + ((smem_chunks + 1) & ~1);   // [kWarps][kChunk] first points of a chunk, per warp
     const int cap = p.cap;
     const bool brk = !p.overflow_continue;
@@ -863,13 +871,16 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
         int sum = 0, esum = 0;
         for (int c = c0; c < c1; ++c) {
             const unsigned int v = __ldcg(p.chunkstat + fr.chunk_off + c);
-            const int ne = __ldcg(p.extn + fr.chunk_off + c);
-            const bool in = c * kChunk < eff;           // (a chunk behind the prefix: zero count, stale list length)
             s_pre[c] = (int)(v & 0xFFFFu);
-            s_epre[c] = in ? ne : 0;
             s_lost[c] = (unsigned short)(v >> 16);
             sum += (int)(v & 0xFFFFu);
-            esum += in ? ne : 0;
+#pragma unroll
+            for (int h = 0; h < kParts; ++h) {
+                // (a part behind the inserted prefix: stale list length)
+                const int ne = c * kChunk + h * kTicket < eff ? __ldcg(p.extn + (size_t)(fr.chunk_off + c) * kParts + h) : 0;
+                s_epre[c * kParts + h] = ne;
+                esum += ne;
+            }
         }
         nch = (eff + kChunk - 1) / kChunk;
         if (threadIdx.x == 0) s_cut = nch - 1;
@@ -877,14 +888,18 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
         int eex = block_exclusive_scan(esum, &etotal, sm);
         int ex = block_exclusive_scan(sum, &total, sm);
         for (int c = c0; c < c1; ++c) {
-            const int v = s_pre[c], ne = s_epre[c];
+            const int v = s_pre[c];
             s_pre[c] = ex;
-            s_epre[c] = eex;
             if (ex <= cap && cap < ex + v) s_cut = c;   // at most one thread: the chunk that holds first point #cap
             ex += v;
-            eex += ne;
+#pragma unroll
+            for (int h = 0; h < kParts; ++h) {
+                const int ne = s_epre[c * kParts + h];
+                s_epre[c * kParts + h] = eex;
+                eex += ne;
+            }
         }
-        if (threadIdx.x == 0) s_epre[fr.nchunks] = etotal;
+        if (threadIdx.x == 0) s_epre[fr.nchunks * kParts] = etotal;
         __syncthreads();
         cut_chunk = s_cut;
         if (publisher) {
@@ -945,24 +960,26 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
             }
             if (BIG && p.T > 1) {
                 // (frames of > 4 M points) the chunk's own extras, by the same warp
-                const int ne = __ldcg(p.extn + cidx);
-                const int2* ext = p.extras + (size_t)cidx * kChunk;
-                for (int j = lane; j < ne; j += 32)
-                    place_two<BIG>(p, fr, f, true, __ldcs(ext + j), false, make_int2(0, 0), s_pre, s_lost);
+                for (int h = 0; h < kParts && c * kChunk + h * kTicket < eff; ++h) {
+                    const int ne = __ldcg(p.extn + (size_t)cidx * kParts + h);
+                    const int2* ext = p.extras + ((size_t)cidx * kParts + h) * kTicket;
+                    for (int j = lane; j < ne; j += 32)
+                        place_two<BIG>(p, fr, f, true, __ldcs(ext + j), false, make_int2(0, 0), s_pre, s_lost);
+                }
             }
         }
     }
     if (BIG || p.T <= 1 || !role3) return;
     // extras of chunks [0, nlim), flattened: item g of the frame belongs to the chunk c with
     // s_epre[c] <= g < s_epre[c + 1]; consecutive lanes take consecutive items, two per lane at a time
-    const int E = s_epre[nlim];
+    const int E = s_epre[nlim * kParts];
     auto fetch = [&](int g) {
-        int lo = 0, hi = nlim - 1;             // largest c with s_epre[c] <= g
+        int lo = 0, hi = nlim * kParts - 1;    // largest list l with s_epre[l] <= g
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
             if (s_epre[mid] <= g) lo = mid; else hi = mid - 1;
         }
-        return __ldcs(p.extras + (size_t)(fr.chunk_off + lo) * kChunk + (g - s_epre[lo]));
+        return __ldcs(p.extras + ((size_t)fr.chunk_off * kParts + lo) * kTicket + (g - s_epre[lo]));
     };
     for (int g0 = w3 * 64; g0 < E; g0 += nw3 * 64) {
         const int ga = g0 + lane, gb = g0 + 32 + lane;
