@@ -1478,6 +1478,20 @@ extern "C" int bvx_frame_stats(bvx_handle* h, int32_t b, int32_t* cells, int32_t
     return BVX_OK;
 }
 
+#ifdef BVX_TIMELINE
+extern "C" int bvx_debug_timeline(unsigned long long* out, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_tl, sizeof(unsigned long long) * 32);
+    if (reset) {
+        unsigned long long init[32];
+        for (int i = 0; i < 32; ++i) init[i] = (i & 1) ? 0ull : ~0ull;
+        cudaMemcpyToSymbol(g_tl, init, sizeof init);
+    }
+    return 0;
+}
+#endif
+
 // ------------------------------------------------------------------ profiling
 extern "C" int bvx_profile_enable(bvx_handle* h, int32_t on)
 {

@@ -178,6 +178,32 @@ __device__ __forceinline__ FrameDesc frame_desc(const Pipe& p, int f)
 // soon as all of its own blocks are resident (the successor's blocks then fill the SM slots the last
 // wave frees), and itself waits here until its predecessor has completed and flushed.  Both
 // instructions are no-ops for a launch without the attribute.
+#ifdef BVX_TIMELINE
+// experiment builds only (tools/variants.sh): first block start / last block end of every kernel role
+__device__ unsigned long long g_tl[32];
+struct TlScope {
+    int k;
+    __device__ __forceinline__ explicit TlScope(int k_) : k(k_)
+    {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (threadIdx.x == 0) atomicMin(&g_tl[2 * k], t);
+    }
+    __device__ __forceinline__ ~TlScope()
+    {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (threadIdx.x == 0) atomicMax(&g_tl[2 * k + 1], t);
+    }
+};
+#define BVX_TL(k) TlScope tl_scope_(k)
+#define BVX_TL_MARK(k) do { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
+        if ((threadIdx.x & 31) == 0) { atomicMin(&g_tl[2 * (k)], t_); atomicMax(&g_tl[2 * (k) + 1], t_); } } while (0)
+#else
+#define BVX_TL(k)
+#define BVX_TL_MARK(k)
+#endif
+
 __device__ __forceinline__ void pdl_prologue()
 {
     asm volatile("griddepcontrol.launch_dependents;");
@@ -367,6 +393,7 @@ __global__ void __launch_bounds__(kIThreads, (CROP ? 4 : BVX_INSERT_BLOCKS) * kP
     const int f = blockIdx.x;
     const FrameDesc fr = frame_desc(p, f);
     FrameState* st = p.state + f;
+    BVX_TL((int)blockIdx.y < p.clear_rows ? 0 : 1);
     // tables already emptied by the previous call's gather (same table regions: its signature is still there)?
     const bool pre = __ldcg(p.counters + 4) == (int)p.tail_sig[0] && __ldcg(p.counters + 5) == (int)p.tail_sig[1];
     if ((int)blockIdx.y < p.clear_rows) {
@@ -834,6 +861,8 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
     __shared__ int sm[kWarps + 1];
     __shared__ int s_cut;
     pdl_prologue();
+    BVX_TL(2);
+    BVX_TL_MARK(7);
     const int f = blockIdx.y;
     const FrameDesc fr = frame_desc(p, f);
     FrameState* st = p.state + f;
@@ -883,6 +912,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
             }
         }
         nch = (eff + kChunk - 1) / kChunk;
+        BVX_TL_MARK(8);
         if (threadIdx.x == 0) s_cut = nch - 1;
         int etotal;
         int eex = block_exclusive_scan(esum, &etotal, sm);
@@ -901,6 +931,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
         }
         if (threadIdx.x == 0) s_epre[fr.nchunks * kParts] = etotal;
         __syncthreads();
+        BVX_TL_MARK(4);
         cut_chunk = s_cut;
         if (publisher) {
             if (threadIdx.x == 0) {
@@ -911,6 +942,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
                 st->rows = 0;
             }
             frames_done(p, sm);
+            BVX_TL_MARK(6);
             return;
         }
     }
@@ -969,6 +1001,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe 
             }
         }
     }
+    BVX_TL_MARK(5);
     if (BIG || p.T <= 1 || !role3) return;
     // extras of chunks [0, nlim), flattened: item g of the frame belongs to the chunk c with
     // s_epre[c] <= g < s_epre[c + 1]; consecutive lanes take consecutive items, two per lane at a time
@@ -1122,6 +1155,7 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
     constexpr int V = kGatherVpt;
     constexpr int TX = T > 1 ? T - 1 : 1;
     pdl_prologue();
+    BVX_TL(3);
     const int f = blockIdx.y;
     const FrameDesc fr = frame_desc(p, f);
     const int nblk = (tiles + V - 1) / V;
