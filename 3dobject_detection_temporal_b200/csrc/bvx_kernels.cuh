@@ -854,8 +854,11 @@ __device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, in
 //   * blocks [n2, gx): the frame's extras, spread evenly over their warps (the chunks' lists are very
 //     uneven: late chunks hold most of them): voxel number of the recorded first point -> slot
 // (one block per frame besides the publisher does both jobs)
+#ifndef BVX_MID_BLOCKS
+#define BVX_MID_BLOCKS 4   // register cap 64 instead of 32: kernel time equal, back-to-back cfg4 step 121.6 -> 118.9 us
+#endif
 template <bool BIG>
-__global__ void __launch_bounds__(kBlock, 8) k_mid(const __grid_constant__ Pipe p, int smem_chunks, int n2)
+__global__ void __launch_bounds__(kBlock, BVX_MID_BLOCKS) k_mid(const __grid_constant__ Pipe p, int smem_chunks, int n2)
 {
     extern __shared__ int s_dyn[];
     __shared__ int sm[kWarps + 1];
