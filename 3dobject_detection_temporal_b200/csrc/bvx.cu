@@ -649,7 +649,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
     size_t gather_smem = 0;
     {
         // general gather: voxels per tile ~256 bucket entries, ~1024 for long buckets (few of their entries are live)
-        int vt = std::max(1, (T > 32 ? 1024 : kBlock) / T);
+        int vt = std::max(1, 1024 / T);            // ~1024 entries per tile: four row reads in flight per thread
         auto tile_smem = [&](int v) {
             return (size_t)(((v * T + 3) & ~3) + 2 * ((v + 3) & ~3)) * 4 + (size_t)v * T * f_out * 4;
         };
@@ -795,10 +795,16 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         }
     } else {
         const int tiles = (cap + gather_vt - 1) / gather_vt;
-        if (gather_smem > 48 * 1024)
-            note(cudaFuncSetAttribute(k_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gather_smem));
         ProfScope ps(h, 5, st);
-        note(launch_k(h, k_gather, dim3(tiles + extra, B), kBlock, gather_smem, st, p, tiles, gather_vt));
+        if (T <= 32) {
+            if (gather_smem > 48 * 1024)
+                note(cudaFuncSetAttribute(k_gather<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gather_smem));
+            note(launch_k(h, k_gather<4>, dim3(tiles + extra, B), kBlock, gather_smem, st, p, tiles, gather_vt));
+        } else {
+            if (gather_smem > 48 * 1024)
+                note(cudaFuncSetAttribute(k_gather<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gather_smem));
+            note(launch_k(h, k_gather<1>, dim3(tiles + extra, B), kBlock, gather_smem, st, p, tiles, gather_vt));
+        }
     }
     if (le != cudaSuccess) return fail(h, BVX_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(le));
     CK(h, cudaGetLastError());

@@ -238,7 +238,7 @@ __device__ __forceinline__ void xform(const SegDesc& sg, float& x, float& y, flo
 // point in a thousand; also NaN, Inf, |t| >= 2^23, a size whose reciprocal is not a normal number: rvs = NaN)
 // the IEEE divide decides: ONE branch per point.
 // -1 if outside / NaN, else the linear cell index in the reference's zyx grid order.
-__device__ __forceinline__ int cell_of(const GridParams& g, float x, float y, float z)
+__device__ __forceinline__ bool cell_xyz(const GridParams& g, float x, float y, float z, int& ix, int& iy, int& iz)
 {
     const float ax = __fsub_rn(x, g.lo[0]), ay = __fsub_rn(y, g.lo[1]), az = __fsub_rn(z, g.lo[2]);
     const float tx = __fmul_rn(ax, g.rvs[0]), ty = __fmul_rn(ay, g.rvs[1]), tz = __fmul_rn(az, g.rvs[2]);
@@ -254,8 +254,15 @@ __device__ __forceinline__ int cell_of(const GridParams& g, float x, float y, fl
     }
     const bool ok = (cx >= 0.0f) && (cx < g.gsf[0]) && (cy >= 0.0f) && (cy < g.gsf[1]) &&
                     (cz >= 0.0f) && (cz < g.gsf[2]);
-    if (!ok) return -1;
-    return ((int)cz * g.gs[1] + (int)cy) * g.gs[0] + (int)cx;
+    ix = (int)cx; iy = (int)cy; iz = (int)cz;
+    return ok;
+}
+
+__device__ __forceinline__ int cell_of(const GridParams& g, float x, float y, float z)
+{
+    int ix, iy, iz;
+    if (!cell_xyz(g, x, y, z, ix, iy, iz)) return -1;
+    return (iz * g.gs[1] + iy) * g.gs[0] + ix;
 }
 
 __device__ __forceinline__ unsigned int hash_cell(unsigned int cell, int shift)
@@ -1108,11 +1115,12 @@ __device__ __forceinline__ void tidy_frame(const Pipe& p, const FrameDesc& fr, i
     }
 }
 
-__device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, int cell)
+// Coordinates of a voxel from its first point (a kept point is in range by construction); no detour over the
+// linear cell index: de-linearising it costs two integer divisions per voxel.
+__device__ __forceinline__ void write_coor(const Pipe& p, int f, size_t gv, float px, float py, float pz)
 {
-    const int gx = p.g.gs[0], gy = p.g.gs[1];
-    const int x = cell % gx, r = cell / gx;
-    const int y = r % gy, z = r / gy;
+    int x, y, z;
+    cell_xyz(p.g, px, py, pz, x, y, z);
     if (p.coor_cols == 4) {
         reinterpret_cast<int4*>(p.coors)[gv] = make_int4(f + p.frame_base, z, y, x);
     } else {
@@ -1279,7 +1287,7 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
         }
         p.num_points[gv] = nvalid[u];
         const float4 r0 = own(0);
-        write_coor(p, f, gv, cell_of(p.g, r0.x, r0.y, r0.z));
+        write_coor(p, f, gv, r0.x, r0.y, r0.z);
         if (p.mean_out) {
             // sum over the T slots in slot order (zeros included), like the reference's features.sum(dim=1)
             float sx = __fadd_rn(0.f, r0.x), sy = __fadd_rn(0.f, r0.y), sz = __fadd_rn(0.f, r0.z), swt = __fadd_rn(0.f, r0.w);
@@ -1305,6 +1313,7 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
 // point + T-1 bucket slots) staged through shared memory; entries are rank-sorted in shared memory
 // (the large-T bucket is unordered).
 // grid (tiles + reset chunks, B); dynamic smem: round4(E) + 2*round4(vt) ints + E*f_out floats, E = vt*T.
+template <int kGB>
 __global__ void __launch_bounds__(kBlock) k_gather(const __grid_constant__ Pipe p, int tiles, int vt)
 {
     extern __shared__ int smem_i[];
@@ -1324,8 +1333,9 @@ __global__ void __launch_bounds__(kBlock) k_gather(const __grid_constant__ Pipe 
     float* srow = reinterpret_cast<float*>(scnt + 2 * ((vt + 3) & ~3));
     const size_t g0 = (size_t)f * p.cap + v0;
     int* gb = p.bucket + g0 * T1;
+    const unsigned int tmagic = (unsigned int)((0x100000000ull + (unsigned)T - 1) / (unsigned)T);   // ceil(2^32 / T) (T = 1: does not fit, handled apart)
     for (int e = threadIdx.x; e < E; e += kBlock) {
-        const int v = e / T, s = e - v * T;
+        const int v = T == 1 ? e : (int)__umulhi((unsigned)e, tmagic), s = e - v * T;
         sidx[e] = s == 0 ? __ldcs(p.vfirst + g0 + v) : gb[(size_t)v * T1 + s - 1];
     }
     __syncthreads();
@@ -1360,25 +1370,70 @@ __global__ void __launch_bounds__(kBlock) k_gather(const __grid_constant__ Pipe 
     }
     __syncthreads();
     const size_t gout = (size_t)p.frame_voxel_offsets[f] + v0;
-    for (int e = threadIdx.x; e < E; e += kBlock) {
-        const int v = e / T, s = e - v * T;
-        const int my = sidx[e];
-        const int nlive = scnt[v], nvalid = snv[v];
-        if (s < nlive && (s == 0 || my < istar)) {
-            const int* vb = sidx + v * T;
-            int r = 0;
-            for (int k = 0; k < nlive; ++k) r += (vb[k] < my);    // slot = rank of the index in the voxel
-            float* dst = srow + (size_t)(v * T + r) * F;
-            fetch_row(p, fr, my, dst);
-            if (p.idx_out) p.idx_out[(gout + v) * T + r] = my;
-            if (r == 0) write_coor(p, f, gout + v, cell_of(p.g, dst[0], dst[1], dst[2]));
+    // Entries in groups of kGB per thread: first every entry of the group finds its slot (rank of its index in the
+    // voxel) and the address of its row (segment, permutation), then all row loads of the group are issued, then the
+    // rows are transformed and stored -- kGB random row reads in flight per thread instead of one (kGB = 4 for T <= 32;
+    // long buckets hold few live entries per tile: kGB = 1 there, measured cfg3 x 64: 921 us against 1251).
+    for (int e0 = 0; e0 < E; e0 += kGB * kBlock) {
+        const float* q[kGB];
+        const SegDesc* sg[kGB];
+        int slot[kGB], vox[kGB];       // slot: (voxel, rank) as voxel * T + rank, -1 = nothing to fetch; vox: voxel if rank 0, else -1
+#pragma unroll
+        for (int k = 0; k < kGB; ++k) {
+            const int e = e0 + k * kBlock + threadIdx.x;
+            slot[k] = -1;
+            if (e >= E) continue;
+            const int v = T == 1 ? e : (int)__umulhi((unsigned)e, tmagic), s = e - v * T;     // e / T, exact for e * T < 2^32
+            const int my = sidx[e];
+            const int nlive = scnt[v], nvalid = snv[v];
+            if (s < nlive && (s == 0 || my < istar)) {
+                const int* vb = sidx + v * T;
+                int r = 0;
+                for (int j = 0; j < nlive; ++j) r += (vb[j] < my);    // slot = rank of the index in the voxel
+                slot[k] = v * T + r;
+                vox[k] = r == 0 ? v : -1;
+                sg[k] = nullptr;
+                if (fr.plain) {
+                    q[k] = plain_rows(p, fr) + (size_t)my * p.f_in;
+                } else {
+                    sg[k] = &find_seg(p, fr, my);
+                    const int jj = sg[k]->perm ? __ldg(sg[k]->perm + (my - sg[k]->start)) : my - sg[k]->start;
+                    q[k] = sg[k]->pts + (size_t)jj * p.f_in;
+                }
+                if (p.idx_out) p.idx_out[(gout + v) * T + r] = my;
+            }
+            if (s >= nvalid) {
+                float* z = srow + (size_t)(v * T + s) * F;
+                for (int j = 0; j < F; ++j) z[j] = 0.0f;
+                if (p.idx_out) p.idx_out[(gout + v) * T + s] = -1;
+            }
+            if (s == 0) p.num_points[gout + v] = nvalid;
         }
-        if (s >= nvalid) {
-            float* z = srow + (size_t)(v * T + s) * F;
-            for (int k = 0; k < F; ++k) z[k] = 0.0f;
-            if (p.idx_out) p.idx_out[(gout + v) * T + s] = -1;
+        float4 r4[kGB];
+        if (p.vec4) {
+#pragma unroll
+            for (int k = 0; k < kGB; ++k)
+                if (slot[k] >= 0) r4[k] = __ldg(reinterpret_cast<const float4*>(q[k]));
         }
-        if (s == 0) p.num_points[gout + v] = nvalid;
+#pragma unroll
+        for (int k = 0; k < kGB; ++k) {
+            if (slot[k] < 0) continue;
+            float* dst = srow + (size_t)slot[k] * F;
+            float x, y, z;
+            if (p.vec4) {
+                x = r4[k].x; y = r4[k].y; z = r4[k].z;
+                dst[3] = r4[k].w;
+            } else {
+                x = __ldg(q[k]); y = __ldg(q[k] + 1); z = __ldg(q[k] + 2);
+                for (int j = 3; j < p.f_in; ++j) dst[j] = __ldg(q[k] + j);
+            }
+            if (sg[k]) {
+                xform(*sg[k], x, y, z);
+                if (sg[k]->has_dt) dst[p.f_in] = sg[k]->dt;
+            }
+            dst[0] = x; dst[1] = y; dst[2] = z;
+            if (vox[k] >= 0) write_coor(p, f, gout + vox[k], x, y, z);
+        }
     }
     __syncthreads();
     float* out = p.voxels + gout * T * F;
