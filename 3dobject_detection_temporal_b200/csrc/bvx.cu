@@ -757,9 +757,9 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         ProfScope ps(h, 1, st);
         // one warp per chunk for the numbering; small batches get up to 4x as many blocks, so that the extras (spread
         // over all warps of a frame) are one round of dependent atomics per warp instead of several; all blocks
-        // resident at once (148 SMs x 8 blocks), + 1 publisher per frame
+        // resident at once (148 SMs x BVX_MID_BLOCKS blocks), + 1 publisher per frame
         const int n2 = std::max(1, (chunks + kWarps - 1) / kWarps);
-        const int gx = std::max(1, std::min(4 * n2, std::max(2, 148 * 8 / B - 1)));
+        const int gx = std::max(1, std::min(4 * n2, std::max(2, 148 * BVX_MID_BLOCKS / B - 1)));
         const int n2e = 0;
         if (chunks > h->scan_smem_chunks) {
             k_scan_big<<<B, kBlock, 0, st>>>(p);

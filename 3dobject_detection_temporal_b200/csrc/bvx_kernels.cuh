@@ -26,6 +26,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef BVX_BULK_LOAD
+#define BVX_BULK_LOAD 0   // k_insert: ticket's points through cp.async.bulk into shared memory (experiment)
+#endif
 #ifndef BVX_TICKET
 #define BVX_TICKET 512     // points per k_insert ticket (block iteration): 1024 or 512
 #endif
@@ -392,10 +395,35 @@ __device__ __forceinline__ void clear_slice(const Pipe& p, const FrameDesc& fr, 
     for (unsigned int j = lo + threadIdx.x; j < hi; j += blockDim.x) t4[j] = e;
 }
 
+#if BVX_BULK_LOAD
+// 1-D bulk copy global -> shared through the TMA unit (cp.async.bulk), completion on an mbarrier
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, unsigned bytes, unsigned long long* bar)
+{
+    const unsigned b = (unsigned)__cvta_generic_to_shared(bar), d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(d), "l"(gsrc), "r"(bytes), "r"(b) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity)
+{
+    const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE;\n\tbra WAIT;\n\tDONE:\n\t}"
+                 ::"r"(b), "r"(parity) : "memory");
+}
+#endif
+
 template <bool CROP>
 __global__ void __launch_bounds__(kIThreads, (CROP ? 4 : BVX_INSERT_BLOCKS) * kParts) k_insert(const __grid_constant__ Pipe p)
 {
     __shared__ int s_tk[2], s_rdy[2], s_extn[2], s_slice;
+#if BVX_BULK_LOAD
+    __shared__ __align__(128) float4 s_pts[2][kTicket];
+    __shared__ __align__(8) unsigned long long s_bar[2];
+#endif
     pdl_prologue();
     const int f = blockIdx.x;
     const FrameDesc fr = frame_desc(p, f);
@@ -436,9 +464,20 @@ __global__ void __launch_bounds__(kIThreads, (CROP ? 4 : BVX_INSERT_BLOCKS) * kP
             c = 0x7FFFFFF;                             // skipped
         }
         s_tk[q] = c;
+#if BVX_BULK_LOAD
+        if (!CROP && fr.plain && p.vec4 && (long long)c * kTicket < fr.n) {
+            // the ticket's points start their way into shared memory now: a barrier earlier than the loads they replace
+            const int np = min(kTicket, fr.n - c * kTicket);
+            bulk_load(s_pts[q], reinterpret_cast<const float4*>(plain_rows(p, fr)) + (size_t)c * kTicket, (unsigned)np * 16u, &s_bar[q]);
+        }
+#endif
     };
     if (threadIdx.x == 0) {
         s_extn[0] = 0; s_extn[1] = 0;
+#if BVX_BULK_LOAD
+        mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+#endif
         take(atomicAdd(&st->ticket, 1ull), 0);
     }
     __syncthreads();
@@ -455,13 +494,22 @@ __global__ void __launch_bounds__(kIThreads, (CROP ? 4 : BVX_INSERT_BLOCKS) * kP
     if (!CROP && fr.plain && p.vec4) {
         // plain frame of float4 points: all four loads are issued before the first one is used
         // (one DRAM round trip per chunk, not four)
-        const float4* qp = reinterpret_cast<const float4*>(plain_rows(p, fr)) + base + toff;
         float4 v[kPts];
+#if BVX_BULK_LOAD
+        mbar_wait(&s_bar[q], (unsigned)(it >> 1) & 1u);
+#pragma unroll
+        for (int k = 0; k < kPts; ++k) {
+            v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (base + toff + k * 32 < fr.n) v[k] = s_pts[q][toff + k * 32];
+        }
+#else
+        const float4* qp = reinterpret_cast<const float4*>(plain_rows(p, fr)) + base + toff;
 #pragma unroll
         for (int k = 0; k < kPts; ++k) {
             v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (base + toff + k * 32 < fr.n) v[k] = __ldcs(qp + k * 32);   // streamed once
         }
+#endif
 #pragma unroll
         for (int k = 0; k < kPts; ++k)
             cell[k] = (base + toff + k * 32 < fr.n) ? cell_of(p.g, v[k].x, v[k].y, v[k].z) : -1;
@@ -862,7 +910,7 @@ __device__ __forceinline__ void place_two(const Pipe& p, const FrameDesc& fr, in
 //     uneven: late chunks hold most of them): voxel number of the recorded first point -> slot
 // (one block per frame besides the publisher does both jobs)
 #ifndef BVX_MID_BLOCKS
-#define BVX_MID_BLOCKS 4   // register cap 64 instead of 32: kernel time equal, back-to-back cfg4 step 121.6 -> 118.9 us
+#define BVX_MID_BLOCKS 6   // resident blocks per SM the launch is sized for (one wave)
 #endif
 template <bool BIG>
 __global__ void __launch_bounds__(kBlock, BVX_MID_BLOCKS) k_mid(const __grid_constant__ Pipe p, int smem_chunks, int n2)
