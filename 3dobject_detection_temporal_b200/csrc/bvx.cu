@@ -449,7 +449,6 @@ struct FrameSpec {
 };
 
 // Chunk rows of k_insert = blocks of one frame in flight at a time (persistent; see run_pipeline).
-static int insert_rows_bound(int B) { return std::max(1, (148 * BVX_INSERT_BLOCKS * kParts + B - 1) / B); }
 
 static int upload_layout(bvx_handle* h, const std::vector<FrameSpec>& frames, cudaStream_t st,
                          int* max_n_out, bool* all_aligned)
@@ -748,10 +747,12 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         // persistent chunk rows: about as many blocks as the GPU holds at once (148 SMs x 8), never
         // more rows than the largest frame has chunks
         const int tickets = (max_n + kTicket - 1) / kTicket;
-        const int rows = std::min(tickets, insert_rows_bound(B));
+        const int occ = crop ? 4 : (p.overflow_continue ? BVX_INSERT_BLOCKS_CONTINUE : BVX_INSERT_BLOCKS);
+        const int rows = std::min(tickets, std::max(1, (148 * occ * kParts + B - 1) / B));
         const dim3 grid(B, p.clear_rows + rows);
-        if (crop) note(launch_k(h, k_insert<true>, grid, kIThreads, 0, st, p));
-        else note(launch_k(h, k_insert<false>, grid, kIThreads, 0, st, p));
+        if (crop) note(launch_k(h, k_insert<true, 4>, grid, kIThreads, 0, st, p));
+        else if (p.overflow_continue) note(launch_k(h, k_insert<false, BVX_INSERT_BLOCKS_CONTINUE>, grid, kIThreads, 0, st, p));
+        else note(launch_k(h, k_insert<false, BVX_INSERT_BLOCKS>, grid, kIThreads, 0, st, p));
     }
     {   // always runs: an empty frame still needs its state and the offsets written
         ProfScope ps(h, 1, st);

@@ -60,8 +60,11 @@ constexpr int kInlineFrames = 64;      // calls of up to this many frames carry 
 #ifndef BVX_GATHER_BLOCKS
 #define BVX_GATHER_BLOCKS 6   // 40 registers; the kernel alone is 1.5 us slower than with 8 blocks of 32, the back-to-back step 6 us faster
 #endif
+#ifndef BVX_INSERT_BLOCKS_CONTINUE
+#define BVX_INSERT_BLOCKS_CONTINUE 8
+#endif
 #ifndef BVX_INSERT_BLOCKS
-#define BVX_INSERT_BLOCKS 6   // 42 registers, no spills: 59.6 us against 76.4 us with 8 blocks of 32 registers (cfg4 break)
+#define BVX_INSERT_BLOCKS 5   // break mode: persistent insert blocks in flight = 148 x 5 x 256 threads (measured 4 / 5 / 6 / 8: see DESIGN)
 #endif
 
 struct GridParams {
@@ -416,8 +419,10 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
 }
 #endif
 
-template <bool CROP>
-__global__ void __launch_bounds__(kIThreads, (CROP ? 4 : BVX_INSERT_BLOCKS) * kParts) k_insert(const __grid_constant__ Pipe p)
+// OCC = resident 256-thread-equivalents per SM the kernel is compiled for (register cap): break mode runs best at 5-6
+// (latency chains of fewer, fatter blocks; less overshoot past the cut-off), continue mode at 8 (more atomics in flight).
+template <bool CROP, int OCC>
+__global__ void __launch_bounds__(kIThreads, OCC * kParts) k_insert(const __grid_constant__ Pipe p)
 {
     __shared__ int s_tk[2], s_rdy[2], s_extn[2], s_slice;
 #if BVX_BULK_LOAD
