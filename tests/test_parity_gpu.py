@@ -809,3 +809,35 @@ def test_errors(pkg):
         pkg.VoxelGenerator([0.0, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5)
     with pytest.raises(RuntimeError):
         pkg.VoxelFeatureExtractorV3()(torch.zeros((3, 5, 4)), torch.ones(3, dtype=torch.int32))
+
+
+@pytest.mark.parametrize("overflow", ["break", "continue"])
+def test_frame_stats(pkg, oracle, synth, overflow):
+    """bvx_frame_stats (what bench.py's `touched bytes` figure is made of): per frame the distinct cells among the points
+    looked at, M, the break cut-off point and the processed prefix, against the same facts derived with numpy."""
+    cap, T = 1200, 5
+    g, o = _pair(pkg, oracle, KITTI, T, cap, overflow)
+    frames = [synth.lidar_frame(n, "kitti", seed=700 + i) for i, n in enumerate([30000, 0, 9000, 2500])]
+    got = g.generate_batched([torch.from_numpy(f).cuda() for f in frames])
+    st = g.frame_stats(len(frames))
+    want = o.generate_batched(frames)
+    lo = np.asarray(KITTI["point_cloud_range"][:3], np.float32)
+    hi = np.asarray(KITTI["point_cloud_range"][3:], np.float32)
+    vs = np.asarray(KITTI["voxel_size"], np.float32)
+    gs = np.round((hi - lo) / vs).astype(np.int64)
+    assert np.array_equal(st["voxels"], np.diff(want[3]))
+    for i, f in enumerate(frames):
+        c = np.floor((f[:, :3] - lo) / vs).astype(np.int64)
+        ok = np.all((c >= 0) & (c < gs), axis=1)
+        key = (c[:, 2] * gs[1] + c[:, 1]) * gs[0] + c[:, 0]
+        idx = np.nonzero(ok)[0]
+        _, first = np.unique(key[idx], return_index=True)
+        firsts = np.sort(idx[first])                      # point index of every cell's first point, in order
+        n = f.shape[0]
+        if overflow == "break" and len(firsts) > cap:
+            assert st["cutoff"][i] == firsts[cap]         # the point that would open voxel number cap
+            assert firsts[cap] < st["processed"][i] <= n and (st["processed"][i] % 512 == 0 or st["processed"][i] == n)
+            assert st["cells"][i] == np.searchsorted(firsts, st["processed"][i])   # cells among the processed prefix
+        else:
+            assert st["processed"][i] == n and st["cutoff"][i] == n
+            assert st["cells"][i] == len(firsts)
