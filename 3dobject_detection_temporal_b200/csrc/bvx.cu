@@ -744,7 +744,7 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
         ProfScope ps(h, 0, st);
         bool crop = false;
         for (const FrameSpec& fs : frames) crop |= fs.crop && fs.crop->n_planes > 0;
-        // persistent chunk rows: about as many blocks as the GPU holds at once (148 SMs x 8), never
+        // persistent ticket rows: 148 SMs x occ x kParts blocks in flight over all frames (occ per mode: DESIGN section 6), never
         // more rows than the largest frame has chunks
         const int tickets = (max_n + kTicket - 1) / kTicket;
         const int occ = crop ? 4 : (p.overflow_continue ? BVX_INSERT_BLOCKS_CONTINUE : BVX_INSERT_BLOCKS);

@@ -2,9 +2,9 @@
 //
 // Pipeline (one pass of VoxelGenerator.generate over B frames; DESIGN.md has the
 // data layout and the per-kernel roofline).  Work is cut into chunks of 1024
-// consecutive points (256 threads x 4 points; a warp owns 128 consecutive points =
-// one "unit" of four 32-point bit words):
-//   k_insert  per chunk : cell key -> table slot; first occurrence by 64-bit
+// consecutive points; a warp owns 128 consecutive points = one "unit" of four 32-point
+// bit words; a k_insert block takes 512 points (4 warps x 4 points per thread) per ticket:
+//   k_insert  per ticket: cell key -> table slot; first occurrence by 64-bit
 //                         atomicCAS/atomicMin on {cell:32 | point index:32};
 //                         candidate bit per point ("held the minimum when I left"),
 //                         `lost` bit for a candidate displaced later; every in-range
