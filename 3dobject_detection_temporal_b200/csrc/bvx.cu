@@ -794,6 +794,17 @@ static int run_pipeline(bvx_handle* h, const std::vector<FrameSpec>& frames, int
             BVX_GS(1) BVX_GS(2) BVX_GS(3) BVX_GS(4) BVX_GS(5) BVX_GS(6) BVX_GS(7) BVX_GS(8)
 #undef BVX_GS
         }
+    } else if (T <= kChainMaxT && vec4 && (f_out == 4 || f_out == 5) && !getenv("BVX_NO_SWEEP_GATHER")) {
+        // frames made of sweeps (transform, dt, permutation, crop): one thread per voxel, T row reads in flight
+        const int tiles = (cap + kBlock - 1) / kBlock;
+        const size_t smem = (size_t)kBlock * T * f_out * 4;
+        const dim3 grid(tiles + extra, B);
+        ProfScope ps(h, 5, st);
+        switch (T) {
+#define BVX_GW(TT) case TT: note(launch_k(h, k_gather_sweeps<TT>, grid, kBlock, smem, st, p, tiles)); break;
+            BVX_GW(1) BVX_GW(2) BVX_GW(3) BVX_GW(4) BVX_GW(5) BVX_GW(6) BVX_GW(7) BVX_GW(8)
+#undef BVX_GW
+        }
     } else {
         const int tiles = (cap + gather_vt - 1) / gather_vt;
         ProfScope ps(h, 5, st);

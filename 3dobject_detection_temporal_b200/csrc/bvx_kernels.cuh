@@ -1362,6 +1362,112 @@ __global__ void __launch_bounds__(kBlock, BVX_GATHER_BLOCKS) k_gather_small(cons
     tidy_frame(p, fr, f);        // last: nothing of this block waits for it
 }
 
+// The same one-thread-per-voxel gather for frames made of SWEEPS (or transformed / permuted / cropped single
+// sweeps): T <= 8, 4 input floats per point in 16-byte aligned rows, F_out = 4 or 5 (dt appended).  The rows
+// cannot go global -> shared asynchronously here -- they are transformed on the way (sweep -> key frame, fixed
+// operation order, no FMA) --, so a thread resolves the addresses of all its T rows (segment, permutation),
+// issues the T loads back to back, then transforms and stages them in the warp's [32 voxels, T, F_out] tile,
+// which goes out coalesced.  (The general k_gather below keeps one to four row reads per thread in flight and
+// spends its time on index arithmetic: cfg5 x 64 frames 983 us there.)
+// grid (tiles of 256 voxels + trailing blocks, B); dynamic smem = kWarps * 32 * T * F_out * 4 bytes.
+template <int T>
+__global__ void __launch_bounds__(kBlock) k_gather_sweeps(const __grid_constant__ Pipe p, int tiles)
+{
+    extern __shared__ float smem_sw[];
+    pdl_prologue();
+    const int f = blockIdx.y;
+    const FrameDesc fr = frame_desc(p, f);
+    if ((int)blockIdx.x >= tiles) { tidy_frame(p, fr, f); tail_block(p, fr, blockIdx.x - tiles); return; }
+    const int F = p.f_out;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int v0 = blockIdx.x * kBlock, v = v0 + threadIdx.x;
+    // the voxel's point indices, fetched before the frame's voxel count is known (see k_gather_small)
+    int idx[T];
+    int* gb = p.bucket + ((size_t)f * p.cap + v) * (T - 1);
+#pragma unroll
+    for (int s = 0; s < T; ++s) idx[s] = kEmptyIdx;
+    if (v < p.cap) {
+        idx[0] = __ldcs(p.vfirst + (size_t)f * p.cap + v);
+#pragma unroll
+        for (int s = 1; s < T; ++s) idx[s] = gb[s - 1];
+    }
+    const int mf = p.state[f].m;
+    const int istar = p.state[f].istar;
+    const size_t gbase = (size_t)p.frame_voxel_offsets[f];
+    if (v0 >= mf) { tidy_frame(p, fr, f); return; }
+    const bool live = v < mf;
+    float4 r4[T];
+    const SegDesc* sg[T];
+    int nvalid = 0;
+#pragma unroll
+    for (int s = 0; s < T; ++s) {
+        int id = live ? idx[s] : kEmptyIdx;
+        if (s > 0) {
+            // a bucket slot that held an entry goes back to empty for the next call; entries behind the
+            // break cut-off i* (a suffix of the row) are dropped
+            if (id != kEmptyIdx) gb[s - 1] = kEmptyIdx;
+            if (id >= istar) id = kEmptyIdx;
+        }
+        idx[s] = id;
+        sg[s] = nullptr;
+        if (id != kEmptyIdx) {
+            ++nvalid;
+            const float* q;
+            if (fr.plain) {
+                q = plain_rows(p, fr) + (size_t)id * 4;
+            } else {
+                sg[s] = &find_seg(p, fr, id);
+                const int jj = sg[s]->perm ? __ldg(sg[s]->perm + (id - sg[s]->start)) : id - sg[s]->start;
+                q = sg[s]->pts + (size_t)jj * 4;
+            }
+            r4[s] = __ldg(reinterpret_cast<const float4*>(q));
+        }
+    }
+    float* sw = smem_sw + (size_t)wid * (32 * T) * F;
+#pragma unroll
+    for (int s = 0; s < T; ++s) {
+        float* dst = sw + (size_t)(lane * T + s) * F;
+        if (idx[s] != kEmptyIdx) {
+            float x = r4[s].x, y = r4[s].y, z = r4[s].z;
+            if (sg[s]) {
+                xform(*sg[s], x, y, z);
+                if (sg[s]->has_dt) dst[4] = sg[s]->dt;
+            }
+            dst[0] = x; dst[1] = y; dst[2] = z; dst[3] = r4[s].w;
+        } else {
+            for (int c = 0; c < F; ++c) dst[c] = 0.0f;
+        }
+    }
+    __syncwarp();
+    if (p.voxels) {
+        const int wv0 = v0 + wid * 32;                    // first voxel of this warp
+        const int wn = min(32, mf - wv0);                 // live voxels of this warp (may be <= 0)
+        float* out = p.voxels + (gbase + wv0) * (size_t)T * F;
+        const int n = wn * T * F;
+        for (int j = lane; j < n; j += 32) __stcs(out + j, sw[j]);
+    }
+    tidy_frame(p, fr, f);
+    if (!live) return;
+    const size_t gv = gbase + v;
+    if (p.idx_out) {
+#pragma unroll
+        for (int s = 0; s < T; ++s) p.idx_out[gv * T + s] = idx[s] == kEmptyIdx ? -1 : idx[s];
+    }
+    p.num_points[gv] = nvalid;
+    const float* own = sw + (size_t)(lane * T) * F;
+    write_coor(p, f, gv, own[0], own[1], own[2]);
+    if (p.mean_out) {
+        // sum over the T slots in slot order (zeros included), like the reference's features.sum(dim=1)
+        const float nf = (float)nvalid;
+        for (int c = 0; c < p.mean_c; ++c) {
+            float sum = 0.0f;
+#pragma unroll
+            for (int s = 0; s < T; ++s) sum = __fadd_rn(sum, own[s * F + c]);
+            p.mean_out[gv * p.mean_c + c] = __fdiv_rn(sum, nf);
+        }
+    }
+}
+
 // General path (any T, any feature count, sweeps): a tile of vt voxels (vt*T entries: the first
 // point + T-1 bucket slots) staged through shared memory; entries are rank-sorted in shared memory
 // (the large-T bucket is unordered).

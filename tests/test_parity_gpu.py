@@ -209,6 +209,11 @@ def test_batched_sweeps(pkg, oracle, synth, overflow):
             gv, gc, gn, goff = g.generate_batched_sweeps(dev_frames)
             assert np.array_equal(goff.cpu().numpy(), woff)
             _eq((gv, gc, gn), (wv, wc, wn), f"batched sweeps T={T}")
+        # fused mean VFE over all five channels (dt included), padded form
+        pv, pc, pn, poff, pmean = g.generate_batched_sweeps(dev_frames, mean_channels=5, padded=True)
+        m = int(woff[-1])
+        _eq((pv[:m], pc[:m], pn[:m]), (wv, wc, wn), f"batched sweeps T={T}, padded + mean")
+        np.testing.assert_allclose(pmean[:m].cpu().numpy(), oracle.mean_vfe(wv, wn, 5), rtol=1e-6, atol=0)
         hv, hc, hn, hoff = g.generate_batched_sweeps(frames)              # numpy in -> numpy out
         assert isinstance(hv, np.ndarray) and np.array_equal(hoff, woff)
         _eq((hv, hc, hn), (wv, wc, wn), "batched sweeps, numpy")
