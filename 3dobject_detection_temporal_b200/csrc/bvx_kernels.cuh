@@ -829,6 +829,9 @@ __device__ __forceinline__ int rank_of(const Pipe& p, const FrameDesc& fr, unsig
         r = s_pre[c];
         nlost = s_lost[c];
     }
+    // requested together with the two loads above (not after their results were used)
+    uint4 lw = make_uint4(0u, 0u, 0u, 0u);
+    if (nlost) lw = __ldcg(reinterpret_cast<const uint4*>(p.lost + fr.word_off + c * kChunkWords + u * kPts));
     // bytes 0 .. u-1 of the eight unit counts
     const unsigned int mlo = u >= 4 ? 0xFFFFFFFFu : ((1u << (8 * u)) - 1u);
     const unsigned int mhi = u <= 4 ? 0u : ((1u << (8 * (u - 4))) - 1u);
@@ -839,7 +842,6 @@ __device__ __forceinline__ int rank_of(const Pipe& p, const FrameDesc& fr, unsig
     r += __popc(cw.x & m0) + __popc(cw.y & m1) + __popc(cw.z & m2) + __popc(cw.w & m3);
     unsigned int mine = wq == 0 ? cw.x : (wq == 1 ? cw.y : (wq == 2 ? cw.z : cw.w));
     if (nlost) {
-        const uint4 lw = __ldcg(reinterpret_cast<const uint4*>(p.lost + fr.word_off + c * kChunkWords + u * kPts));
         r -= (int)__vsadu4(u8.z & mlo, 0u) + (int)__vsadu4(u8.w & mhi, 0u);
         r -= __popc(lw.x & m0) + __popc(lw.y & m1) + __popc(lw.z & m2) + __popc(lw.w & m3);
         mine &= ~(wq == 0 ? lw.x : (wq == 1 ? lw.y : (wq == 2 ? lw.z : lw.w)));
@@ -961,17 +963,21 @@ __global__ void __launch_bounds__(kBlock, BVX_MID_BLOCKS) k_mid(const __grid_con
         const int c0 = min(fr.nchunks, (int)threadIdx.x * per), c1 = min(fr.nchunks, c0 + per);
         eff = min(fr.n, __ldcg(&st->n_eff));     // prefix that went through k_insert
         int sum = 0, esum = 0;
+        // the list lengths are requested together with n_eff and the counts, and the ones of parts behind the
+        // inserted prefix (stale values of an earlier call) are dropped afterwards: one round trip, not two
         for (int c = c0; c < c1; ++c) {
             const unsigned int v = __ldcg(p.chunkstat + fr.chunk_off + c);
+            int ne[kParts];
+#pragma unroll
+            for (int h = 0; h < kParts; ++h) ne[h] = __ldcg(p.extn + (size_t)(fr.chunk_off + c) * kParts + h);
             s_pre[c] = (int)(v & 0xFFFFu);
             s_lost[c] = (unsigned short)(v >> 16);
             sum += (int)(v & 0xFFFFu);
 #pragma unroll
             for (int h = 0; h < kParts; ++h) {
-                // (a part behind the inserted prefix: stale list length)
-                const int ne = c * kChunk + h * kTicket < eff ? __ldcg(p.extn + (size_t)(fr.chunk_off + c) * kParts + h) : 0;
-                s_epre[c * kParts + h] = ne;
-                esum += ne;
+                if (c * kChunk + h * kTicket >= eff) ne[h] = 0;
+                s_epre[c * kParts + h] = ne[h];
+                esum += ne[h];
             }
         }
         nch = (eff + kChunk - 1) / kChunk;
